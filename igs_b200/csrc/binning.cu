@@ -1,0 +1,335 @@
+// binning.cu — instance generation, stable radix sort, tile ranges.
+//
+// Replaces reference K2-K5 (DGR/cuda_rasterizer/rasterizer_impl.cu:350-391: cub InclusiveSum,
+// duplicateWithKeys :70-111, cub SortPairs on 64-bit (tile|depth) keys :376-381, identifyTileRanges
+// :151-173).  The reference sorts R instances on ~45-bit keys (6 radix passes over 12-byte pairs).
+// Here the same permutation is produced by a two-level stable sort:
+//   A. sort the V*P Gaussians by (view, depth bits)               — 4-5 passes over V*P pairs
+//   B. emit instances in that order (row-major tiles per Gaussian, exactly the reference's emission
+//      order inside one Gaussian) and stable-sort them by global tile id only — 2-3 passes over R
+// A stable sort by tile of a depth-ordered list equals a stable sort by (tile, depth) with ties in
+// ascending Gaussian index, which is what CUB's stable LSD sort yields for the reference
+// (SURVEY T8/T9); tests compare the decoded 64-bit keys / point_list / ranges bit-for-bit.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace igs {
+
+// ---------------------------------------------------------------------------------------------
+// Exclusive scan (u32), two launches: block sums, then scan-with-lookback-by-summation.
+// ---------------------------------------------------------------------------------------------
+#define SCAN_THREADS 256
+#define SCAN_ITEMS 8
+#define SCAN_TILE (SCAN_THREADS * SCAN_ITEMS)  // 2048, must match scan_blocks()
+
+__device__ __forceinline__ uint32_t warp_incl_scan(uint32_t v) {
+#pragma unroll
+  for (int o = 1; o < 32; o <<= 1) {
+    uint32_t t = __shfl_up_sync(0xffffffffu, v, o);
+    if (lane_id() >= (uint32_t)o) v += t;
+  }
+  return v;
+}
+
+__device__ __forceinline__ uint32_t block_reduce_sum(uint32_t v, uint32_t* smem /*>=8*/) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  __syncthreads();
+  if (lane_id() == 0) smem[threadIdx.x >> 5] = v;
+  __syncthreads();
+  uint32_t t = 0;
+#pragma unroll
+  for (int w = 0; w < SCAN_THREADS / 32; w++) t += smem[w];
+  return t;
+}
+
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_block_sums_kernel(const uint32_t* __restrict__ in, size_t n, uint32_t* __restrict__ sums) {
+  __shared__ uint32_t sm[8];
+  size_t base = (size_t)blockIdx.x * SCAN_TILE;
+  uint32_t s = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) {
+    size_t i = base + (size_t)k * SCAN_THREADS + threadIdx.x;
+    if (i < n) s += in[i];
+  }
+  s = block_reduce_sum(s, sm);
+  if (threadIdx.x == 0) sums[blockIdx.x] = s;
+}
+
+// out may alias in.  If total != nullptr the grand total is written by the last block.
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_apply_kernel(const uint32_t* in, size_t n, const uint32_t* __restrict__ sums, uint32_t* out,
+                  uint32_t* __restrict__ total) {
+  __shared__ uint32_t sm[8];
+  __shared__ uint32_t wsum[SCAN_THREADS / 32];
+  // base = sum of all previous block sums
+  uint32_t b = 0;
+  for (uint32_t j = threadIdx.x; j < blockIdx.x; j += SCAN_THREADS) b += sums[j];
+  b = block_reduce_sum(b, sm);
+
+  size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+  uint32_t v[SCAN_ITEMS];
+  uint32_t tsum = 0;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) {
+    size_t i = base + k;
+    v[k] = (i < n) ? in[i] : 0u;
+    tsum += v[k];
+  }
+  uint32_t incl = warp_incl_scan(tsum);
+  if (lane_id() == 31) wsum[threadIdx.x >> 5] = incl;
+  __syncthreads();
+  uint32_t woff = 0;
+#pragma unroll
+  for (int w = 0; w < SCAN_THREADS / 32; w++)
+    if (w < (int)(threadIdx.x >> 5)) woff += wsum[w];
+  uint32_t run = b + woff + incl - tsum;
+#pragma unroll
+  for (int k = 0; k < SCAN_ITEMS; k++) {
+    size_t i = base + k;
+    if (i < n) out[i] = run;
+    run += v[k];
+  }
+  if (total != nullptr && blockIdx.x == gridDim.x - 1 && threadIdx.x == SCAN_THREADS - 1) *total = run;
+}
+
+void launch_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint32_t* block_sums,
+                           uint32_t* total, cudaStream_t s) {
+  if (n == 0) return;
+  unsigned nb = (unsigned)scan_blocks(n);
+  scan_block_sums_kernel<<<nb, SCAN_THREADS, 0, s>>>(in, n, block_sums);
+  scan_apply_kernel<<<nb, SCAN_THREADS, 0, s>>>(in, n, block_sums, out, total);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Stable LSD radix sort, 8-bit digits, 256 threads x 16 keys per block.
+// ---------------------------------------------------------------------------------------------
+template <typename K>
+__device__ __forceinline__ uint32_t digit_of(K key, int shift, uint32_t mask) {
+  return (uint32_t)(key >> shift) & mask;
+}
+
+template <typename K>
+__global__ void __launch_bounds__(IGS_SORT_THREADS)
+radix_hist_kernel(const K* __restrict__ keys, size_t n, int shift, uint32_t mask, uint32_t* __restrict__ hist,
+                  unsigned nblocks) {
+  __shared__ uint32_t h[256];
+  h[threadIdx.x] = 0;
+  __syncthreads();
+  size_t base = (size_t)blockIdx.x * IGS_SORT_TILE;
+#pragma unroll
+  for (int k = 0; k < IGS_SORT_ITEMS; k++) {
+    size_t i = base + (size_t)k * IGS_SORT_THREADS + threadIdx.x;
+    if (i < n) atomicAdd(&h[digit_of<K>(keys[i], shift, mask)], 1u);
+  }
+  __syncthreads();
+  hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+}
+
+// Each warp ranks a contiguous chunk of 512 keys in 16 rounds of 32 consecutive keys, so that the
+// rank order equals the index order (stability).
+template <typename K>
+__global__ void __launch_bounds__(IGS_SORT_THREADS)
+radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, K* __restrict__ keys_out,
+                     uint32_t* __restrict__ vals_out, size_t n, int shift, uint32_t mask,
+                     const uint32_t* __restrict__ hist_scanned, unsigned nblocks) {
+  constexpr int WARPS = IGS_SORT_THREADS / 32;
+  constexpr int CHUNK = IGS_SORT_TILE / WARPS;      // 512 keys per warp
+  constexpr int ROUNDS = CHUNK / 32;                // 16
+  __shared__ uint32_t whist[WARPS][257];
+  const int w = threadIdx.x >> 5;
+  const uint32_t lane = lane_id();
+  for (int i = threadIdx.x; i < WARPS * 257; i += IGS_SORT_THREADS) (&whist[0][0])[i] = 0;
+  __syncthreads();
+
+  const size_t wbase = (size_t)blockIdx.x * IGS_SORT_TILE + (size_t)w * CHUNK;
+  K key[ROUNDS];
+  uint32_t rnk[ROUNDS];
+  uint32_t dig[ROUNDS];
+#pragma unroll
+  for (int r = 0; r < ROUNDS; r++) {
+    size_t i = wbase + (size_t)r * 32 + lane;
+    bool valid = i < n;
+    key[r] = valid ? keys_in[i] : K(0);
+    uint32_t d = valid ? digit_of<K>(key[r], shift, mask) : 256u;
+    dig[r] = d;
+    uint32_t peers = __match_any_sync(0xffffffffu, d);
+    uint32_t lt = peers & ((1u << lane) - 1u);
+    int leader = __ffs(peers) - 1;
+    uint32_t old = 0;
+    if ((int)lane == leader) {
+      old = whist[w][d];
+      whist[w][d] = old + __popc(peers);
+    }
+    old = __shfl_sync(0xffffffffu, old, leader);
+    rnk[r] = old + __popc(lt);
+    __syncwarp();
+  }
+  __syncthreads();
+  // cross-warp exclusive scan per digit; thread d owns digit d
+  {
+    uint32_t d = threadIdx.x;
+    uint32_t run = hist_scanned[(size_t)d * nblocks + blockIdx.x];
+#pragma unroll
+    for (int ww = 0; ww < WARPS; ww++) {
+      uint32_t c = whist[ww][d];
+      whist[ww][d] = run;
+      run += c;
+    }
+  }
+  __syncthreads();
+#pragma unroll
+  for (int r = 0; r < ROUNDS; r++) {
+    size_t i = wbase + (size_t)r * 32 + lane;
+    if (i < n) {
+      uint32_t pos = whist[w][dig[r]] + rnk[r];
+      keys_out[pos] = key[r];
+      vals_out[pos] = vals_in[i];
+    }
+  }
+}
+
+// Sorts n (key,value) pairs on key bits [0, end_bit).  Buffers ping-pong; returns the index (0/1)
+// of the buffer pair that holds the sorted result.
+template <typename K>
+int radix_sort_pairs(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint32_t* hist,
+                     uint32_t* scan_tmp_unused, cudaStream_t s) {
+  (void)scan_tmp_unused;
+  if (n == 0) return 0;
+  unsigned nb = (unsigned)sort_blocks(n);
+  int cur = 0;
+  // the scan of the [256][nb] histogram needs its own block-sum scratch; it lives behind the histogram
+  uint32_t* hsums = hist + (size_t)256 * nb;
+  (void)hsums;
+  for (int shift = 0; shift < end_bit; shift += 8) {
+    int bits = end_bit - shift < 8 ? end_bit - shift : 8;
+    uint32_t mask = (1u << bits) - 1u;
+    radix_hist_kernel<K><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], n, shift, mask, hist, nb);
+    // in-place exclusive scan over the bin-major histogram
+    launch_exclusive_scan(hist, hist, (size_t)256 * nb, hist + (size_t)256 * nb, nullptr, s);
+    radix_scatter_kernel<K><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
+                                                            shift, mask, hist, nb);
+    cur ^= 1;
+  }
+  return cur;
+}
+
+template int radix_sort_pairs<uint64_t>(uint64_t* keys[2], uint32_t* vals[2], size_t, int, uint32_t*, uint32_t*, cudaStream_t);
+template int radix_sort_pairs<uint32_t>(uint32_t* keys[2], uint32_t* vals[2], size_t, int, uint32_t*, uint32_t*, cudaStream_t);
+
+// ---------------------------------------------------------------------------------------------
+// After sort A: tiles in depth order + inverse permutation
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+gather_rank_kernel(size_t VP, const uint32_t* __restrict__ sorted_gid, const uint32_t* __restrict__ tiles,
+                   uint32_t* __restrict__ tiles_sorted /*[VP+1]*/, uint32_t* __restrict__ rank) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i > VP) return;
+  if (i == VP) { tiles_sorted[i] = 0; return; }
+  uint32_t gid = sorted_gid[i];
+  tiles_sorted[i] = tiles[gid];
+  rank[gid] = (uint32_t)i;
+}
+
+void launch_gather_rank(size_t VP, const uint32_t* sorted_gid, const uint32_t* tiles, uint32_t* tiles_sorted,
+                        uint32_t* rank, cudaStream_t s) {
+  unsigned nb = (unsigned)((VP + 1 + 255) / 256);
+  gather_rank_kernel<<<nb, 256, 0, s>>>(VP, sorted_gid, tiles, tiles_sorted, rank);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Instance emission (reference duplicateWithKeys, rasterizer_impl.cu:70-111, getRect auxiliary.h:62-72)
+// One thread per depth-sorted Gaussian; emission slot e = inst_off[i] + row-major tile index.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tile_rect(float px, float py, int radius, int tiles_x, int tiles_y, int& x0, int& y0,
+                                          int& x1, int& y1) {
+  float rf = (float)radius;
+  x0 = min(tiles_x, max(0, (int)fmul(fsub(px, rf), 0.0625f)));
+  y0 = min(tiles_y, max(0, (int)fmul(fsub(py, rf), 0.0625f)));
+  x1 = min(tiles_x, max(0, (int)fmul(fadd(fadd(fadd(px, rf), 16.0f), -1.0f), 0.0625f)));
+  y1 = min(tiles_y, max(0, (int)fmul(fadd(fadd(fadd(py, rf), 16.0f), -1.0f), 0.0625f)));
+}
+
+__global__ void __launch_bounds__(256)
+emit_instances_kernel(size_t VP, uint32_t P, int tiles_x, int tiles_y, const uint32_t* __restrict__ sorted_gid,
+                      const uint32_t* __restrict__ inst_off, const SplatHead* __restrict__ head,
+                      const int* __restrict__ radii, uint32_t* __restrict__ tkey, uint32_t* __restrict__ tval,
+                      uint32_t* __restrict__ inst_gid) {
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= VP) return;
+  uint32_t off = inst_off[i];
+  uint32_t n = inst_off[i + 1] - off;
+  if (n == 0) return;
+  uint32_t gid = sorted_gid[i];
+  uint32_t v = gid / P;
+  float4 h = head[gid].a;
+  int x0, y0, x1, y1;
+  tile_rect(h.x, h.y, radii[gid], tiles_x, tiles_y, x0, y0, x1, y1);
+  uint32_t tbase = v * (uint32_t)(tiles_x * tiles_y);
+  for (int y = y0; y < y1; y++)
+    for (int x = x0; x < x1; x++) {
+      tkey[off] = tbase + (uint32_t)(y * tiles_x + x);
+      tval[off] = off;
+      inst_gid[off] = gid;
+      off++;
+    }
+}
+
+void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, const uint32_t* sorted_gid,
+                           const uint32_t* inst_off, const SplatHead* head, const int* radii, uint32_t* tkey,
+                           uint32_t* tval, uint32_t* inst_gid, cudaStream_t s) {
+  if (VP == 0) return;
+  unsigned nb = (unsigned)((VP + 255) / 256);
+  emit_instances_kernel<<<nb, 256, 0, s>>>(VP, P, tiles_x, tiles_y, sorted_gid, inst_off, head, radii, tkey, tval,
+                                           inst_gid);
+}
+
+// ---------------------------------------------------------------------------------------------
+// After sort B: tile ranges (reference identifyTileRanges) + sorted Gaussian-id list
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+finalize_bins_kernel(uint32_t R, const uint32_t* __restrict__ tkey, const uint32_t* __restrict__ point_e,
+                     const uint32_t* __restrict__ inst_gid, uint32_t* __restrict__ point_list,
+                     uint2* __restrict__ ranges) {
+  uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= R) return;
+  uint32_t t = tkey[j];
+  if (j == 0) {
+    ranges[t].x = 0;
+  } else {
+    uint32_t tp = tkey[j - 1];
+    if (t != tp) {
+      ranges[tp].y = j;
+      ranges[t].x = j;
+    }
+  }
+  if (j == R - 1) ranges[t].y = R;
+  point_list[j] = inst_gid[point_e[j]];
+}
+
+void launch_finalize_bins(uint32_t R, const uint32_t* tkey, const uint32_t* point_e, const uint32_t* inst_gid,
+                          uint32_t* point_list, uint2* ranges, cudaStream_t s) {
+  if (R == 0) return;
+  finalize_bins_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, tkey, point_e, inst_gid, point_list, ranges);
+}
+
+// Decode helper for tests: 64-bit reference-style keys in sorted order.
+__global__ void decode_keys_kernel(uint32_t R, uint32_t tiles_per_view, uint32_t P, const uint32_t* __restrict__ tkey,
+                                   const uint32_t* __restrict__ point_list, const float* __restrict__ depth,
+                                   uint64_t* __restrict__ keys, uint32_t* __restrict__ plist_local) {
+  uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
+  if (j >= R) return;
+  uint32_t gid = point_list[j];
+  if (keys) keys[j] = ((uint64_t)(tkey[j] % tiles_per_view) << 32) | __float_as_uint(depth[gid]);
+  if (plist_local) plist_local[j] = gid % P;
+}
+
+void launch_decode_keys(uint32_t R, uint32_t tiles_per_view, uint32_t P, const uint32_t* tkey,
+                        const uint32_t* point_list, const float* depth, uint64_t* keys, uint32_t* plist_local,
+                        cudaStream_t s) {
+  if (R == 0) return;
+  decode_keys_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, tiles_per_view, P, tkey, point_list, depth, keys, plist_local);
+}
+
+}  // namespace igs

@@ -1,0 +1,244 @@
+// blend_fwd.cu — forward tile blending (colour / expected+median coord / expected+median depth /
+// normal / weight), replacing the reference's forward renderCUDA (DGR/cuda_rasterizer/forward.cu:428-693).
+//
+// One CTA per (view, 16x16 tile); each of its 8 warps owns an 8x4 pixel block.  Per batch of up to
+// 256 instances of the tile's depth-sorted list:
+//   1. every thread fetches one instance's 32-B head and tests it against the tile with a
+//      conservative bounding box of the alpha >= 1/255 ellipse; survivors are compacted IN ORDER
+//      into shared memory together with their list position (the reference's `contributor` counts
+//      every visited instance, SURVEY T12, so positions — not compacted indices — are kept);
+//   2. survivors' 64-B tails are fetched;
+//   3. each warp tests 32 survivors at a time against its own 8x4 block (one lane per survivor),
+//      ballots, and only the hits are evaluated per pixel.
+// The per-pixel arithmetic that decides alpha / T / termination is pinned to the reference's
+// compiled operation order (common.cuh splat_power; expf, not __expf), so n_contrib is bit-exact.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace igs {
+
+
+#define BLEND_BATCH 256
+
+// Conservative half-extents of { d : alpha(d) >= 1/255 } for conic (A,B,C) and opacity o.
+// Returns false if the splat can never reach alpha >= 1/255.  Non-PSD / non-finite conics get
+// infinite extents (never culled) so the exact per-pixel test decides.
+__device__ __forceinline__ bool alpha_extent(float A, float B, float C, float o, float& ex, float& ey) {
+  if (o < 0.00392156862f) return false;  // o*G <= o < 1/255 for every G in [0,1]
+  float det = A * C - B * B;
+  float tau = __logf(255.0f * o) * 1.0005f + 1e-3f;
+  ex = ey = 3.0e38f;
+  if (det > 0.0f && A > 0.0f && C > 0.0f) {
+    float k = 2.0f * tau / det;
+    float x2 = k * C, y2 = k * A;
+    if (x2 < 1e30f && y2 < 1e30f) {
+      ex = sqrtf(x2) * 1.0005f + 0.01f;
+      ey = sqrtf(y2) * 1.0005f + 0.01f;
+    }
+  }
+  return true;
+}
+
+template <bool COORD, bool DEPTH, bool NORMAL>
+__global__ void __launch_bounds__(256)
+blend_fwd_kernel(BlendFwdParams p) {
+  constexpr bool GEO = COORD || DEPTH || NORMAL;
+  __shared__ float4 s_ha[BLEND_BATCH];   // x, y, conic.x, conic.y
+  __shared__ float4 s_hb[BLEND_BATCH];   // conic.z, opacity, r, g
+  __shared__ float2 s_ext[BLEND_BATCH];
+  __shared__ uint32_t s_gid[BLEND_BATCH];
+  __shared__ uint32_t s_pos[BLEND_BATCH];
+  __shared__ float4 s_t[GEO ? BLEND_BATCH * 4 : BLEND_BATCH];
+  __shared__ uint32_t s_wcount[8];
+
+  const int tiles = p.tiles_x * p.tiles_y;
+  const int gt = blockIdx.x;
+  const int v = gt / tiles;
+  const int t = gt - v * tiles;
+  const int tyi = t / p.tiles_x, txi = t - tyi * p.tiles_x;
+  const int w = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int wx0 = txi * IGS_TILE_X + (w & 1) * 8;
+  const int wy0 = tyi * IGS_TILE_Y + (w >> 1) * 4;
+  const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
+  const bool inside = pxi < p.W && pyi < p.H;
+  const size_t N = (size_t)p.W * p.H;
+  const size_t pix_id = (size_t)p.W * pyi + pxi;
+  const float pixfx = (float)pxi, pixfy = (float)pyi;
+  // tile bounds in pixel-centre coordinates (clipped to the image)
+  const float tx0 = (float)(txi * IGS_TILE_X), ty0 = (float)(tyi * IGS_TILE_Y);
+  const float tx1 = (float)(min(txi * IGS_TILE_X + IGS_TILE_X, p.W) - 1);
+  const float ty1 = (float)(min(tyi * IGS_TILE_Y + IGS_TILE_Y, p.H) - 1);
+  const float bx0 = (float)wx0, by0 = (float)wy0;
+  const float bx1 = (float)(wx0 + 7), by1 = (float)(wy0 + 3);
+
+  const uint2 range = p.ranges[gt];
+  bool done = !inside;
+
+  float T = 1.0f;
+  uint32_t last_contributor = 0, max_contributor = 0xFFFFFFFFu;
+  float C0 = 0, C1 = 0, C2 = 0, weight = 0;
+  float Co0 = 0, Co1 = 0, Co2 = 0, mCo0 = 0, mCo1 = 0, mCo2 = 0;
+  float Depth = 0, mDepth = 0;
+  float N0 = 0, N1 = 0, N2 = 0;
+
+  for (uint32_t start = range.x; start < range.y; start += BLEND_BATCH) {
+    if (__syncthreads_count(done) == 256) break;
+    // ---- 1. fetch + tile-level cull + ordered compaction ----
+    uint32_t j = start + threadIdx.x;
+    bool keep = false;
+    float4 ha, hb;
+    float ex = 0, ey = 0;
+    uint32_t gid = 0;
+    if (j < range.y) {
+      gid = p.point_list[j];
+      ha = p.head[gid].a;
+      hb = p.head[gid].b;
+      keep = alpha_extent(ha.z, ha.w, hb.x, hb.y, ex, ey);
+      keep = keep && (ha.x + ex >= tx0) && (ha.x - ex <= tx1) && (ha.y + ey >= ty0) && (ha.y - ey <= ty1);
+    }
+    uint32_t bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_wcount[w] = __popc(bal);
+    __syncthreads();
+    uint32_t woff = 0, count = 0;
+#pragma unroll
+    for (int ww = 0; ww < 8; ww++) {
+      uint32_t c = s_wcount[ww];
+      if (ww < w) woff += c;
+      count += c;
+    }
+    if (keep) {
+      uint32_t k = woff + __popc(bal & ((1u << lane) - 1u));
+      s_ha[k] = ha;
+      s_hb[k] = hb;
+      s_ext[k] = make_float2(ex, ey);
+      s_gid[k] = gid;
+      s_pos[k] = j - range.x + 1;  // 1-based position = reference `contributor`
+    }
+    __syncthreads();
+    // ---- 2. tails of the survivors ----
+    if constexpr (GEO) {
+      for (uint32_t f = threadIdx.x; f < count * 4; f += 256) {
+        uint32_t k = f >> 2, q = f & 3;
+        s_t[f] = reinterpret_cast<const float4*>(p.tail + s_gid[k])[q];
+      }
+    } else {
+      if (threadIdx.x < count) s_t[threadIdx.x].x = p.tail[s_gid[threadIdx.x]].a.x;  // blue
+    }
+    __syncthreads();
+    // ---- 3. per-warp cull + blend ----
+    if (!__all_sync(0xffffffffu, done)) {
+      for (uint32_t base = 0; base < count; base += 32) {
+        uint32_t k = base + lane;
+        bool hit = false;
+        if (k < count) {
+          float4 a = s_ha[k];
+          float2 e = s_ext[k];
+          hit = (a.x + e.x >= bx0) && (a.x - e.x <= bx1) && (a.y + e.y >= by0) && (a.y - e.y <= by1);
+        }
+        uint32_t m = __ballot_sync(0xffffffffu, hit);
+        while (m) {
+          int b = __ffs(m) - 1;
+          m &= m - 1;
+          uint32_t kk = base + b;
+          if (done) continue;
+          float4 a = s_ha[kk];
+          float4 bq = s_hb[kk];
+          float dx = fsub(a.x, pixfx), dy = fsub(a.y, pixfy);
+          float power = splat_power(dx, dy, a.z, a.w, bq.x);
+          if (power > 0.0f) continue;
+          float alpha = fminf(0.99f, fmul(bq.y, expf(power)));
+          if (alpha < 1.0f / 255.0f) continue;
+          float test_T = fmul(T, fsub(1.0f, alpha));
+          if (test_T < 0.0001f) { done = true; continue; }
+          float aT = fmul(alpha, T);
+          uint32_t contributor = s_pos[kk];
+          float blue;
+          bool before_median = T > 0.5f;
+          if constexpr (GEO) {
+            float4 t0 = s_t[kk * 4 + 0], t1 = s_t[kk * 4 + 1], t2 = s_t[kk * 4 + 2], t3 = s_t[kk * 4 + 3];
+            blue = t0.x;
+            if constexpr (COORD) {
+              float c0 = ffma(dy, t2.w, ffma(dx, t2.z, t1.w));
+              float c1 = ffma(dy, t3.y, ffma(dx, t3.x, t2.x));
+              float c2 = ffma(dy, t3.w, ffma(dx, t3.z, t2.y));
+              Co0 = ffma(aT, c0, Co0); Co1 = ffma(aT, c1, Co1); Co2 = ffma(aT, c2, Co2);
+              if (before_median) { mCo0 = c0; mCo1 = c1; mCo2 = c2; }
+            }
+            if constexpr (DEPTH) {
+              float tt = t0.y + (t0.z * dx + t0.w * dy);
+              Depth += tt * aT;
+              if (before_median) mDepth = tt;
+            }
+            if constexpr (NORMAL) {
+              N0 += t1.x * aT; N1 += t1.y * aT; N2 += t1.z * aT;
+            }
+            if (before_median) max_contributor = contributor;
+          } else {
+            blue = s_t[kk].x;
+          }
+          C0 = ffma(aT, bq.z, C0); C1 = ffma(aT, bq.w, C1); C2 = ffma(aT, blue, C2);
+          weight += aT;
+          T = test_T;
+          last_contributor = contributor;
+        }
+        if (__all_sync(0xffffffffu, done)) break;
+      }
+    }
+  }
+
+  if (inside) {
+    p.n_contrib[(size_t)v * 2 * N + pix_id] = last_contributor;
+    p.n_contrib[(size_t)v * 2 * N + N + pix_id] = max_contributor;
+    float* oc = p.out_color + (size_t)v * 3 * N;
+    oc[pix_id] = C0 + T * p.bg[0];
+    oc[N + pix_id] = C1 + T * p.bg[1];
+    oc[2 * N + pix_id] = C2 + T * p.bg[2];
+    p.out_alpha[(size_t)v * N + pix_id] = weight;
+    if constexpr (GEO) {
+      const float pnx = (pixfx - p.W / 2.f) / p.focal_x, pny = (pixfy - p.H / 2.f) / p.focal_y;
+      const float ln = sqrtf(pnx * pnx + pny * pny + 1.0f);
+      if constexpr (COORD) {
+        float* o = p.out_coord + (size_t)v * 3 * N;
+        float* om = p.out_mcoord + (size_t)v * 3 * N;
+        float* ac = p.accum_coord + (size_t)v * 3 * N;
+        if (last_contributor) {
+          o[pix_id] = Co0 / weight; o[N + pix_id] = Co1 / weight; o[2 * N + pix_id] = Co2 / weight;
+        } else {
+          o[pix_id] = 0; o[N + pix_id] = 0; o[2 * N + pix_id] = 0;
+        }
+        ac[pix_id] = Co0; ac[N + pix_id] = Co1; ac[2 * N + pix_id] = Co2;
+        om[pix_id] = mCo0; om[N + pix_id] = mCo1; om[2 * N + pix_id] = mCo2;
+      }
+      if constexpr (DEPTH) {
+        float depth_ln = Depth / ln;
+        p.accum_depth[(size_t)v * N + pix_id] = depth_ln;
+        p.out_depth[(size_t)v * N + pix_id] = last_contributor ? depth_ln / weight : 0.0f;
+        p.out_mdepth[(size_t)v * N + pix_id] = mDepth / ln;
+      }
+      if constexpr (NORMAL) {
+        float* on = p.out_normal + (size_t)v * 3 * N;
+        if (last_contributor) {
+          float len = sqrtf(N0 * N0 + N1 * N1 + N2 * N2);
+          p.normal_length[(size_t)v * N + pix_id] = len;
+          len = fmaxf(len, IGS_NORMALIZE_EPS);
+          on[pix_id] = N0 / len; on[N + pix_id] = N1 / len; on[2 * N + pix_id] = N2 / len;
+        } else {
+          p.normal_length[(size_t)v * N + pix_id] = 1.0f;
+          on[pix_id] = 0; on[N + pix_id] = 0; on[2 * N + pix_id] = 0;
+        }
+      }
+    }
+  }
+}
+
+void launch_blend_fwd(const BlendFwdParams& p, int V, bool coord, bool depth, cudaStream_t s) {
+  int nblocks = V * p.tiles_x * p.tiles_y;
+  if (nblocks <= 0) return;
+  if (coord && depth) blend_fwd_kernel<true, true, true><<<nblocks, 256, 0, s>>>(p);
+  else if (coord && !depth) blend_fwd_kernel<true, false, true><<<nblocks, 256, 0, s>>>(p);
+  else if (!coord && depth) blend_fwd_kernel<false, true, true><<<nblocks, 256, 0, s>>>(p);
+  else blend_fwd_kernel<false, false, false><<<nblocks, 256, 0, s>>>(p);
+}
+
+}  // namespace igs

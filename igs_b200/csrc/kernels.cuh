@@ -1,0 +1,127 @@
+// kernels.cuh — parameter blocks and host launchers shared between api.cu and the kernel files.
+#pragma once
+#include "common.cuh"
+
+namespace igs {
+
+struct ProjectParams {
+  int P, V, D, M;
+  int W, H;
+  int tiles_x, tiles_y;
+  float tan_fovx, tan_fovy, focal_x, focal_y, kernel_size;
+  const float* means3D;
+  const float* opacities;
+  const float* shs;
+  const float* colors_precomp;
+};
+
+struct BlendFwdParams {
+  int W, H, tiles_x, tiles_y;
+  float focal_x, focal_y;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const SplatHead* head;
+  const SplatTail* tail;
+  const float* bg;
+  float* out_color;
+  float* out_coord;
+  float* out_mcoord;
+  float* out_depth;
+  float* out_mdepth;
+  float* out_alpha;
+  float* out_normal;
+  uint32_t* n_contrib;
+  float* accum_coord;
+  float* accum_depth;
+  float* normal_length;
+};
+
+struct BlendBwdParams {
+  int W, H, tiles_x, tiles_y;
+  float focal_x, focal_y;
+  const uint2* ranges;
+  const uint32_t* point_list;
+  const uint32_t* point_e;
+  const SplatHead* head;
+  const SplatTail* tail;
+  const float* bg;
+  const float* alphas;
+  const float* normalmap;
+  const uint32_t* n_contrib;
+  const float* accum_coord;
+  const float* accum_depth;
+  const float* normal_length;
+  const float* dL_color;
+  const float* dL_coord;
+  const float* dL_mcoord;
+  const float* dL_depth;
+  const float* dL_mdepth;
+  const float* dL_alpha;
+  const float* dL_normal;
+  float* grec;  // [R][NS]
+};
+
+struct GatherBwdParams {
+  int P, V, W, H;
+  int ns;  // floats per record (16 or 32)
+  float focal_x, focal_y, tan_fovx, tan_fovy, kernel_size;
+  const float* means3D;
+  const Camera* cams;
+  const float* cov3D;
+  const GaussEig* eig;
+  const SplatHead* head;
+  const int* radii;
+  const uint32_t* tiles;
+  const uint32_t* rank;
+  const uint32_t* inst_off;
+  const uint8_t* clamped;
+  const float* grec;
+  float* dL_dmeans2D;  // [V*P][3]
+  float* partial;      // [V*P][16]: dmean3, dcov6, dRGB3(clamp applied), dopacity, rawRGB3
+};
+
+struct FinishBwdParams {
+  int P, V, D, M;
+  float scale_modifier;
+  const float* means3D;
+  const float* shs;
+  const float* scales;
+  const float* rotations;
+  const Camera* cams;
+  const int* radii;
+  const float* partial;
+  float* dL_dmeans3D;
+  float* dL_dcov3D;
+  float* dL_dopacity;
+  float* dL_dcolors;
+  float* dL_dsh;
+  float* dL_dscales;
+  float* dL_drotations;
+};
+
+void launch_gauss_setup(int P, const float* scales, float mod, const float* rotations, const float* cov3D_precomp,
+                        float* cov3D_out, GaussEig* eig, cudaStream_t s);
+void launch_project(const ProjectParams& p, const GeomBuf& g, int* radii_out, cudaStream_t s);
+void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s);
+
+void launch_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint32_t* block_sums, uint32_t* total,
+                           cudaStream_t s);
+template <typename K>
+int radix_sort_pairs(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint32_t* hist, uint32_t* unused,
+                     cudaStream_t s);
+void launch_gather_rank(size_t VP, const uint32_t* sorted_gid, const uint32_t* tiles, uint32_t* tiles_sorted,
+                        uint32_t* rank, cudaStream_t s);
+void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, const uint32_t* sorted_gid,
+                           const uint32_t* inst_off, const SplatHead* head, const int* radii, uint32_t* tkey,
+                           uint32_t* tval, uint32_t* inst_gid, cudaStream_t s);
+void launch_finalize_bins(uint32_t R, const uint32_t* tkey, const uint32_t* point_e, const uint32_t* inst_gid,
+                          uint32_t* point_list, uint2* ranges, cudaStream_t s);
+void launch_decode_keys(uint32_t R, uint32_t tiles_per_view, uint32_t P, const uint32_t* tkey,
+                        const uint32_t* point_list, const float* depth, uint64_t* keys, uint32_t* plist_local,
+                        cudaStream_t s);
+void launch_blend_fwd(const BlendFwdParams& p, int V, bool coord, bool depth, cudaStream_t s);
+void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s);
+void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s);
+void launch_finish_bwd(const FinishBwdParams& p, cudaStream_t s);
+
+}  // namespace igs

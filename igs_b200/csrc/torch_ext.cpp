@@ -1,0 +1,321 @@
+// torch_ext.cpp — thin PyTorch glue over the C-ABI (include/igs_raster.h).
+//
+// Exposes the reference's pybind entry points with identical names, argument order and return
+// tuples (DGR/ext.cpp:15-19, DGR/rasterize_points.h:18-81):
+//   rasterize_gaussians, rasterize_gaussians_backward, mark_visible
+// plus the batched V-view variants used by the multi-view refine step and a fused Adam step.
+// Tensors are only used for memory ownership and stream lookup; all compute is in libigs_raster.so.
+#include <torch/extension.h>
+#include <ATen/cuda/CUDAContext.h>
+#include <c10/cuda/CUDAGuard.h>
+#include <tuple>
+#include <vector>
+#include "../../include/igs_raster.h"
+
+namespace {
+
+char* tensor_alloc(void* user, size_t bytes) {
+  auto* t = reinterpret_cast<torch::Tensor*>(user);
+  t->resize_({(long long)bytes});
+  return reinterpret_cast<char*>(t->data_ptr());
+}
+
+const float* fptr(const torch::Tensor& t, const char* name) {
+  if (!t.defined() || t.numel() == 0) return nullptr;
+  TORCH_CHECK(t.is_cuda(), name, " must be a CUDA tensor (this rasterizer has no CPU path)");
+  TORCH_CHECK(t.scalar_type() == torch::kFloat32, name, " must be float32");
+  TORCH_CHECK(t.is_contiguous(), name, " must be contiguous");
+  return t.data_ptr<float>();
+}
+
+torch::Tensor contig(const torch::Tensor& t) {
+  if (!t.defined() || t.numel() == 0) return t;
+  return t.contiguous();
+}
+
+void check(int rc, const char* what) {
+  if (rc != IGS_OK) {
+    std::string msg = std::string(what) + " failed: " + igs_last_error();
+    if (rc == IGS_ERR_INVALID || rc == IGS_ERR_UNSUPPORTED) throw std::runtime_error(msg);
+    throw std::runtime_error(msg);
+  }
+}
+
+using FwdRet = std::tuple<int, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+                          torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor>;
+
+// Shared implementation for V >= 1.  `batched` only changes output shapes ([V,C,H,W] vs [C,H,W]).
+FwdRet forward_impl(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                    const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                    float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                    const torch::Tensor& projmatrix, float tan_fovx, float tan_fovy, float kernel_size, int H, int W,
+                    const torch::Tensor& sh, int degree, const torch::Tensor& campos, bool prefiltered,
+                    bool require_coord, bool require_depth, bool debug, int V, bool batched) {
+  if (means3D.ndimension() != 2 || means3D.size(1) != 3) {
+    AT_ERROR("means3D must have dimensions (num_points, 3)");
+  }
+  TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (this rasterizer has no CPU path)");
+  const c10::cuda::CUDAGuard guard(means3D.device());
+  const int P = (int)means3D.size(0);
+  auto fopt = means3D.options().dtype(torch::kFloat32);
+  auto iopt = means3D.options().dtype(torch::kInt32);
+  auto shape = [&](int C) { return batched ? std::vector<int64_t>{V, C, H, W} : std::vector<int64_t>{C, H, W}; };
+  // one zero-filled slab for the 15 output planes (the reference zero-fills 8 tensors separately)
+  torch::Tensor slab = torch::zeros({(int64_t)V * 15, H, W}, fopt);
+  int64_t plane = (int64_t)H * W;
+  auto view_of = [&](int64_t first, int C) {
+    return slab.narrow(0, first, (int64_t)V * C).view(shape(C));
+  };
+  torch::Tensor out_color = view_of(0, 3);
+  torch::Tensor out_coord = view_of((int64_t)V * 3, 3);
+  torch::Tensor out_mcoord = view_of((int64_t)V * 6, 3);
+  torch::Tensor out_normal = view_of((int64_t)V * 9, 3);
+  torch::Tensor out_depth = view_of((int64_t)V * 12, 1);
+  torch::Tensor out_mdepth = view_of((int64_t)V * 13, 1);
+  torch::Tensor out_alpha = view_of((int64_t)V * 14, 1);
+  (void)plane;
+  torch::Tensor radii = batched ? torch::zeros({V, P}, iopt) : torch::zeros({P}, iopt);
+
+  auto bopt = torch::TensorOptions().dtype(torch::kByte).device(means3D.device());
+  torch::Tensor geomBuffer = torch::empty({0}, bopt);
+  torch::Tensor binningBuffer = torch::empty({0}, bopt);
+  torch::Tensor imgBuffer = torch::empty({0}, bopt);
+
+  int rendered = 0;
+  if (P != 0) {
+    int M = 0;
+    if (sh.defined() && sh.numel() != 0) M = (int)sh.size(1);
+    torch::Tensor bg = contig(background), m3 = contig(means3D), col = contig(colors), op = contig(opacity),
+                  sc = contig(scales), rot = contig(rotations), c3 = contig(cov3D_precomp), vm = contig(viewmatrix),
+                  pm = contig(projmatrix), shc = contig(sh), cp = contig(campos);
+    igs_forward_args a;
+    memset(&a, 0, sizeof(a));
+    a.P = P; a.D = degree; a.M = M; a.V = V; a.width = W; a.height = H;
+    a.background = fptr(bg, "bg"); a.means3D = fptr(m3, "means3D"); a.shs = fptr(shc, "sh");
+    a.colors_precomp = fptr(col, "colors_precomp"); a.opacities = fptr(op, "opacities");
+    a.scales = fptr(sc, "scales"); a.scale_modifier = scale_modifier; a.rotations = fptr(rot, "rotations");
+    a.cov3D_precomp = fptr(c3, "cov3D_precomp"); a.viewmatrix = fptr(vm, "viewmatrix");
+    a.projmatrix = fptr(pm, "projmatrix"); a.cam_pos = fptr(cp, "campos");
+    a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.kernel_size = kernel_size;
+    a.prefiltered = prefiltered; a.require_coord = require_coord; a.require_depth = require_depth; a.debug = debug;
+    a.out_color = out_color.data_ptr<float>(); a.out_coord = out_coord.data_ptr<float>();
+    a.out_mcoord = out_mcoord.data_ptr<float>(); a.out_depth = out_depth.data_ptr<float>();
+    a.out_mdepth = out_mdepth.data_ptr<float>(); a.out_alpha = out_alpha.data_ptr<float>();
+    a.out_normal = out_normal.data_ptr<float>(); a.radii = radii.data_ptr<int>();
+    TORCH_CHECK(a.background && a.opacities && a.viewmatrix && a.projmatrix && a.cam_pos, "missing required CUDA input");
+    TORCH_CHECK(vm.numel() == (int64_t)V * 16 && pm.numel() == (int64_t)V * 16 && cp.numel() == (int64_t)V * 3,
+                "camera tensors must hold ", V, " view(s)");
+    if (a.colors_precomp == nullptr && a.shs == nullptr) throw std::runtime_error("For non-RGB, provide precomputed Gaussian colors!");
+    cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+    check(igs_rasterize_forward(&a, tensor_alloc, &geomBuffer, tensor_alloc, &binningBuffer, tensor_alloc, &imgBuffer,
+                                (void*)stream, &rendered),
+          "rasterize_gaussians");
+  }
+  return std::make_tuple(rendered, out_color, out_coord, out_mcoord, out_alpha, out_normal, out_depth, out_mdepth, radii,
+                         geomBuffer, binningBuffer, imgBuffer);
+}
+
+using BwdRet = std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
+                          torch::Tensor, torch::Tensor>;
+
+BwdRet backward_impl(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+                     const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
+                     float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
+                     const torch::Tensor& projmatrix, float tan_fovx, float tan_fovy, float kernel_size,
+                     const torch::Tensor& dL_dout_color, const torch::Tensor& dL_dout_coord,
+                     const torch::Tensor& dL_dout_mcoord, const torch::Tensor& dL_dout_depth,
+                     const torch::Tensor& dL_dout_mdepth, const torch::Tensor& dL_dout_alpha,
+                     const torch::Tensor& dL_dout_normal, const torch::Tensor& normalmap, const torch::Tensor& sh,
+                     int degree, const torch::Tensor& campos, const torch::Tensor& geomBuffer, int R,
+                     const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const torch::Tensor& alphas,
+                     bool require_coord, bool require_depth, bool debug, int V, bool batched) {
+  TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (this rasterizer has no CPU path)");
+  const c10::cuda::CUDAGuard guard(means3D.device());
+  const int P = (int)means3D.size(0);
+  const int H = (int)alphas.size(-2), W = (int)alphas.size(-1);
+  int M = 0;
+  if (sh.defined() && sh.numel() != 0) M = (int)sh.size(1);
+  auto fopt = means3D.options().dtype(torch::kFloat32);
+  torch::Tensor dL_dmeans3D = torch::empty({P, 3}, fopt);
+  torch::Tensor dL_dmeans2D = batched ? torch::empty({V, P, 3}, fopt) : torch::empty({P, 3}, fopt);
+  torch::Tensor dL_dcolors = torch::empty({P, 3}, fopt);
+  torch::Tensor dL_dopacity = torch::empty({P, 1}, fopt);
+  torch::Tensor dL_dcov3D = torch::empty({P, 6}, fopt);
+  torch::Tensor dL_dsh = torch::empty({P, M, 3}, fopt);
+  torch::Tensor dL_dscales = torch::zeros({P, 3}, fopt);
+  torch::Tensor dL_drotations = torch::zeros({P, 4}, fopt);
+  if (P != 0) {
+    torch::Tensor bg = contig(background), m3 = contig(means3D), col = contig(colors), sc = contig(scales),
+                  rot = contig(rotations), c3 = contig(cov3D_precomp), vm = contig(viewmatrix), pm = contig(projmatrix),
+                  shc = contig(sh), cp = contig(campos), rd = contig(radii), al = contig(alphas), nm = contig(normalmap);
+    torch::Tensor gc = contig(dL_dout_color), gco = contig(dL_dout_coord), gmc = contig(dL_dout_mcoord),
+                  gd = contig(dL_dout_depth), gmd = contig(dL_dout_mdepth), ga = contig(dL_dout_alpha),
+                  gn = contig(dL_dout_normal);
+    if (!gc.defined() || gc.numel() == 0) gc = torch::zeros({(int64_t)V * 3, H, W}, fopt);
+    igs_backward_args a;
+    memset(&a, 0, sizeof(a));
+    a.P = P; a.D = degree; a.M = M; a.V = V; a.R = R; a.width = W; a.height = H;
+    a.background = fptr(bg, "bg"); a.means3D = fptr(m3, "means3D"); a.shs = fptr(shc, "sh");
+    a.colors_precomp = fptr(col, "colors_precomp"); a.scales = fptr(sc, "scales"); a.scale_modifier = scale_modifier;
+    a.rotations = fptr(rot, "rotations"); a.cov3D_precomp = fptr(c3, "cov3D_precomp");
+    a.viewmatrix = fptr(vm, "viewmatrix"); a.projmatrix = fptr(pm, "projmatrix"); a.cam_pos = fptr(cp, "campos");
+    a.tan_fovx = tan_fovx; a.tan_fovy = tan_fovy; a.kernel_size = kernel_size;
+    TORCH_CHECK(rd.is_cuda() && rd.scalar_type() == torch::kInt32, "radii must be a CUDA int32 tensor");
+    a.radii = rd.data_ptr<int>(); a.alphas = fptr(al, "alphas"); a.normalmap = fptr(nm, "normalmap");
+    a.geom_buffer = reinterpret_cast<char*>(geomBuffer.data_ptr());
+    a.binning_buffer = reinterpret_cast<char*>(binningBuffer.data_ptr());
+    a.image_buffer = reinterpret_cast<char*>(imageBuffer.data_ptr());
+    a.dL_dout_color = fptr(gc, "grad_color"); a.dL_dout_coord = fptr(gco, "grad_coord");
+    a.dL_dout_mcoord = fptr(gmc, "grad_mcoord"); a.dL_dout_depth = fptr(gd, "grad_depth");
+    a.dL_dout_mdepth = fptr(gmd, "grad_mdepth"); a.dL_dout_alpha = fptr(ga, "grad_alpha");
+    a.dL_dout_normal = fptr(gn, "grad_normal");
+    a.dL_dmeans2D = dL_dmeans2D.data_ptr<float>(); a.dL_dcolors = dL_dcolors.data_ptr<float>();
+    a.dL_dopacity = dL_dopacity.data_ptr<float>(); a.dL_dmeans3D = dL_dmeans3D.data_ptr<float>();
+    a.dL_dcov3D = dL_dcov3D.data_ptr<float>(); a.dL_dsh = M ? dL_dsh.data_ptr<float>() : nullptr;
+    a.dL_dscales = a.scales ? dL_dscales.data_ptr<float>() : nullptr;
+    a.dL_drotations = a.scales ? dL_drotations.data_ptr<float>() : nullptr;
+    a.require_coord = require_coord; a.require_depth = require_depth; a.debug = debug;
+    auto bopt = torch::TensorOptions().dtype(torch::kByte).device(means3D.device());
+    torch::Tensor temp = torch::empty({0}, bopt);
+    cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+    check(igs_rasterize_backward(&a, tensor_alloc, &temp, (void*)stream), "rasterize_gaussians_backward");
+  }
+  return std::make_tuple(dL_dmeans2D, dL_dcolors, dL_dopacity, dL_dmeans3D, dL_dcov3D, dL_dsh, dL_dscales, dL_drotations);
+}
+
+}  // namespace
+
+// ---- reference-compatible entry points (single view) ----
+FwdRet RasterizeGaussiansCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                              const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                              const float scale_modifier, const torch::Tensor& cov3D_precomp,
+                              const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix, const float tan_fovx,
+                              const float tan_fovy, const float kernel_size, const int image_height,
+                              const int image_width, const torch::Tensor& sh, const int degree,
+                              const torch::Tensor& campos, const bool prefiltered, const bool require_coord,
+                              const bool require_depth, const bool debug) {
+  return forward_impl(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                      projmatrix, tan_fovx, tan_fovy, kernel_size, image_height, image_width, sh, degree, campos,
+                      prefiltered, require_coord, require_depth, debug, 1, false);
+}
+
+BwdRet RasterizeGaussiansBackwardCUDA(
+    const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+    const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations, const float scale_modifier,
+    const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix, const torch::Tensor& projmatrix,
+    const float tan_fovx, const float tan_fovy, const float kernel_size, const torch::Tensor& dL_dout_color,
+    const torch::Tensor& dL_dout_coord, const torch::Tensor& dL_dout_mcoord, const torch::Tensor& dL_dout_depth,
+    const torch::Tensor& dL_dout_mdepth, const torch::Tensor& dL_dout_alpha, const torch::Tensor& dL_dout_normal,
+    const torch::Tensor& normalmap, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+    const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer,
+    const torch::Tensor& alphas, const bool require_coord, const bool require_depth, const bool debug) {
+  return backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrix,
+                       projmatrix, tan_fovx, tan_fovy, kernel_size, dL_dout_color, dL_dout_coord, dL_dout_mcoord,
+                       dL_dout_depth, dL_dout_mdepth, dL_dout_alpha, dL_dout_normal, normalmap, sh, degree, campos,
+                       geomBuffer, R, binningBuffer, imageBuffer, alphas, require_coord, require_depth, debug, 1, false);
+}
+
+torch::Tensor markVisible(torch::Tensor& means3D, torch::Tensor& viewmatrix, torch::Tensor& projmatrix) {
+  TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (this rasterizer has no CPU path)");
+  const c10::cuda::CUDAGuard guard(means3D.device());
+  const int P = (int)means3D.size(0);
+  torch::Tensor present = torch::full({P}, false, means3D.options().dtype(at::kBool));
+  if (P != 0) {
+    torch::Tensor m3 = means3D.contiguous(), vm = viewmatrix.contiguous(), pm = projmatrix.contiguous();
+    check(igs_mark_visible(P, fptr(m3, "means3D"), fptr(vm, "viewmatrix"), fptr(pm, "projmatrix"),
+                           reinterpret_cast<uint8_t*>(present.data_ptr<bool>()),
+                           (void*)at::cuda::getCurrentCUDAStream().stream()),
+          "mark_visible");
+  }
+  return present;
+}
+
+// ---- batched multi-view entry points (V cameras sharing H, W, tan_fov) ----
+FwdRet RasterizeViewsCUDA(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& colors,
+                          const torch::Tensor& opacity, const torch::Tensor& scales, const torch::Tensor& rotations,
+                          const float scale_modifier, const torch::Tensor& cov3D_precomp,
+                          const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices, const float tan_fovx,
+                          const float tan_fovy, const float kernel_size, const int image_height, const int image_width,
+                          const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+                          const bool prefiltered, const bool require_coord, const bool require_depth, const bool debug) {
+  TORCH_CHECK(viewmatrices.dim() == 3, "viewmatrices must be [V,4,4]");
+  return forward_impl(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
+                      viewmatrices, projmatrices, tan_fovx, tan_fovy, kernel_size, image_height, image_width, sh, degree,
+                      campos, prefiltered, require_coord, require_depth, debug, (int)viewmatrices.size(0), true);
+}
+
+BwdRet RasterizeViewsBackwardCUDA(
+    const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
+    const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations, const float scale_modifier,
+    const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices,
+    const float tan_fovx, const float tan_fovy, const float kernel_size, const torch::Tensor& dL_dout_color,
+    const torch::Tensor& dL_dout_coord, const torch::Tensor& dL_dout_mcoord, const torch::Tensor& dL_dout_depth,
+    const torch::Tensor& dL_dout_mdepth, const torch::Tensor& dL_dout_alpha, const torch::Tensor& dL_dout_normal,
+    const torch::Tensor& normalmap, const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
+    const torch::Tensor& geomBuffer, const int R, const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer,
+    const torch::Tensor& alphas, const bool require_coord, const bool require_depth, const bool debug) {
+  return backward_impl(background, means3D, radii, colors, scales, rotations, scale_modifier, cov3D_precomp, viewmatrices,
+                       projmatrices, tan_fovx, tan_fovy, kernel_size, dL_dout_color, dL_dout_coord, dL_dout_mcoord,
+                       dL_dout_depth, dL_dout_mdepth, dL_dout_alpha, dL_dout_normal, normalmap, sh, degree, campos,
+                       geomBuffer, R, binningBuffer, imageBuffer, alphas, require_coord, require_depth, debug,
+                       (int)viewmatrices.size(0), true);
+}
+
+// Decode the opaque buffers into reference-style arrays (parity tests).
+std::vector<torch::Tensor> DecodeBuffers(int P, int V, int R, int H, int W, const torch::Tensor& geomBuffer,
+                                         const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer) {
+  const c10::cuda::CUDAGuard guard(geomBuffer.device());
+  auto dev = geomBuffer.device();
+  auto fo = torch::TensorOptions().dtype(torch::kFloat32).device(dev);
+  auto io = torch::TensorOptions().dtype(torch::kInt32).device(dev);
+  auto lo = torch::TensorOptions().dtype(torch::kInt64).device(dev);
+  int tiles = ((W + 15) / 16) * ((H + 15) / 16);
+  torch::Tensor keys = torch::zeros({R}, lo), plist = torch::zeros({R}, io), ranges = torch::zeros({V * tiles, 2}, io),
+                ncontrib = torch::zeros({V, 2, H * W}, io), tiles_t = torch::zeros({V, P}, io),
+                depths = torch::zeros({V, P}, fo), means2D = torch::zeros({V, P, 2}, fo),
+                conic = torch::zeros({V, P, 4}, fo), rgb = torch::zeros({V, P, 3}, fo), cov3D = torch::zeros({P, 6}, fo),
+                vp = torch::zeros({V, P, 3}, fo), cpl = torch::zeros({V, P, 6}, fo), rp = torch::zeros({V, P, 2}, fo),
+                ts = torch::zeros({V, P}, fo), nrm = torch::zeros({V, P, 3}, fo);
+  igs_decode_out o;
+  o.keys = reinterpret_cast<uint64_t*>(keys.data_ptr<int64_t>());
+  o.point_list = reinterpret_cast<uint32_t*>(plist.data_ptr<int>());
+  o.ranges = reinterpret_cast<uint32_t*>(ranges.data_ptr<int>());
+  o.n_contrib = reinterpret_cast<uint32_t*>(ncontrib.data_ptr<int>());
+  o.tiles_touched = reinterpret_cast<uint32_t*>(tiles_t.data_ptr<int>());
+  o.depths = depths.data_ptr<float>(); o.means2D = means2D.data_ptr<float>(); o.conic_opacity = conic.data_ptr<float>();
+  o.rgb = rgb.data_ptr<float>(); o.cov3D = cov3D.data_ptr<float>(); o.view_points = vp.data_ptr<float>();
+  o.camera_planes = cpl.data_ptr<float>(); o.ray_planes = rp.data_ptr<float>(); o.ts = ts.data_ptr<float>();
+  o.normals = nrm.data_ptr<float>();
+  check(igs_decode_binning(P, V, R, W, H, reinterpret_cast<const char*>(geomBuffer.data_ptr()),
+                           R > 0 ? reinterpret_cast<const char*>(binningBuffer.data_ptr()) : nullptr,
+                           reinterpret_cast<const char*>(imageBuffer.data_ptr()), &o,
+                           (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "decode_buffers");
+  return {keys, plist, ranges, ncontrib, tiles_t, depths, means2D, conic, rgb, cov3D, vp, cpl, rp, ts, nrm};
+}
+
+void AdamStep(torch::Tensor& param, const torch::Tensor& grad, torch::Tensor& exp_avg, torch::Tensor& exp_avg_sq,
+              double lr, double beta1, double beta2, double eps, int64_t step) {
+  TORCH_CHECK(param.is_cuda() && grad.is_cuda() && exp_avg.is_cuda() && exp_avg_sq.is_cuda(), "Adam tensors must be CUDA");
+  TORCH_CHECK(param.is_contiguous() && grad.is_contiguous() && exp_avg.is_contiguous() && exp_avg_sq.is_contiguous(),
+              "Adam tensors must be contiguous");
+  TORCH_CHECK(param.scalar_type() == torch::kFloat32 && grad.scalar_type() == torch::kFloat32, "Adam tensors must be float32");
+  TORCH_CHECK(param.numel() == grad.numel() && param.numel() == exp_avg.numel() && param.numel() == exp_avg_sq.numel(),
+              "Adam tensor sizes differ");
+  const c10::cuda::CUDAGuard guard(param.device());
+  check(igs_adam_step(param.data_ptr<float>(), grad.data_ptr<float>(), exp_avg.data_ptr<float>(),
+                      exp_avg_sq.data_ptr<float>(), (size_t)param.numel(), (float)lr, (float)beta1, (float)beta2,
+                      (float)eps, (int)step, (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "adam_step");
+}
+
+PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
+  m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
+  m.def("mark_visible", &markVisible);
+  m.def("rasterize_views", &RasterizeViewsCUDA);
+  m.def("rasterize_views_backward", &RasterizeViewsBackwardCUDA);
+  m.def("decode_buffers", &DecodeBuffers);
+  m.def("adam_step", &AdamStep);
+  m.def("abi_version", []() { return igs_abi_version(); });
+}

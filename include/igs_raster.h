@@ -1,0 +1,204 @@
+/*
+ * igs_raster.h — C-ABI of the B200-native differentiable Gaussian-splat rasterizer.
+ *
+ * This is the drop-in boundary for the one hot path of IGS's per-key-frame refine loop
+ * (reference: /root/reference/infer_batch.py:279-324).  Every entry point below replaces one
+ * reference interface; `DGR/` abbreviates
+ * submodules/RaDe-GS/submodules/diff-gaussian-rasterization/ in the reference tree.
+ *
+ *   igs_rasterize_forward   <- CudaRasterizer::Rasterizer::forward   (DGR/cuda_rasterizer/rasterizer.h:31-63,
+ *                                                                     DGR/cuda_rasterizer/rasterizer_impl.cu:254-425)
+ *                              as called by RasterizeGaussiansCUDA    (DGR/rasterize_points.cu:35-133)
+ *   igs_rasterize_backward  <- CudaRasterizer::Rasterizer::backward  (DGR/cuda_rasterizer/rasterizer.h:65-110,
+ *                                                                     DGR/cuda_rasterizer/rasterizer_impl.cu:429-571)
+ *                              as called by RasterizeGaussiansBackwardCUDA (DGR/rasterize_points.cu:135-246)
+ *   igs_mark_visible        <- CudaRasterizer::Rasterizer::markVisible (DGR/cuda_rasterizer/rasterizer.h:24-29,
+ *                                                                     DGR/cuda_rasterizer/rasterizer_impl.cu:176-188)
+ *   igs_decode_binning      <- (test/inspection only) exposes what the reference keeps in BinningState /
+ *                              ImageState (DGR/cuda_rasterizer/rasterizer_impl.h:64-86): sorted 64-bit keys,
+ *                              point_list, tile ranges, n_contrib.
+ *   igs_adam_step           <- torch.optim.Adam(eps=1e-15) over the refine parameters
+ *                              (igs/models/gaussian_model.py:348; infer_batch.py:323)
+ *
+ * Conventions
+ *   - All pointers are DEVICE pointers unless stated otherwise; float = IEEE fp32; layouts are the
+ *     reference's: means3D [P][3], shs [P][M][3], scales [P][3], rotations [P][4] (r,x,y,z; NOT
+ *     normalised inside, reference forward.cu:279), opacities [P], cov3D_precomp [P][6],
+ *     colors_precomp [P][3], image maps [V][C][H][W].
+ *   - A NULL pointer means "absent", exactly as the reference branches on nullptr
+ *     (rasterizer_impl.cu:394,540; forward.cu:363,407; backward.cu:622,626).
+ *   - V (num_views) generalises the reference's one-view call: viewmatrix/projmatrix/cam_pos hold
+ *     V cameras ([V][16], [V][16], [V][3], reference row-vector convention) that share W, H and
+ *     tan_fov; outputs and radii get a leading [V] dimension.  V == 1 is bit-for-bit the reference call.
+ *     In backward, per-Gaussian gradients are SUMMED over the V views (one refine step on V views).
+ *   - Scratch memory is owned by the caller and obtained through igs_alloc_fn callbacks, mirroring
+ *     the reference's std::function<char*(size_t)> resize functionals (rasterize_points.cu:27-33).
+ *     The three forward buffers are opaque, self-describing (header + (P,V,R,W*H)) and must be handed
+ *     back unchanged to igs_rasterize_backward (reference: ctx.save_for_backward,
+ *     diff_gaussian_rasterization_rade/__init__.py:98-100).
+ *   - All work is enqueued on `stream` (a cudaStream_t passed as void*).  The only host
+ *     synchronisation in forward is one 8-byte D2H read of the instance count (the reference has the
+ *     same one, rasterizer_impl.cu:354).
+ *   - Return value: 0 on success, negative igs_status otherwise.  igs_last_error() gives a message.
+ *     There is NO CPU fallback: without a CUDA device every compute entry point returns
+ *     IGS_ERR_CUDA.
+ */
+#ifndef IGS_RASTER_H_INCLUDED
+#define IGS_RASTER_H_INCLUDED
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define IGS_RASTER_ABI_VERSION 1
+
+typedef enum igs_status {
+  IGS_OK = 0,
+  IGS_ERR_INVALID = -1,     /* bad argument (reference: AT_ERROR / std::runtime_error)            */
+  IGS_ERR_CUDA = -2,        /* CUDA runtime error (reference: thrown only when debug=true)        */
+  IGS_ERR_UNSUPPORTED = -3, /* e.g. prefiltered=true or M > 16                       */
+  IGS_ERR_ALLOC = -4        /* allocator callback returned NULL                                    */
+} igs_status;
+
+/* Scratch allocator: must return a device pointer to at least `bytes` bytes, 256-B aligned,
+ * valid until the matching backward has run.  `user` is passed through unchanged. */
+typedef char* (*igs_alloc_fn)(void* user, size_t bytes);
+
+typedef struct igs_forward_args {
+  int P;              /* number of Gaussians                                        */
+  int D;              /* active SH degree (0..3)                                    */
+  int M;              /* SH coefficients per Gaussian stored in `shs` (<= 16)       */
+  int V;              /* number of camera views (>= 1)                              */
+  int width, height;  /* image size shared by all V views                           */
+  const float* background;     /* [3]                                               */
+  const float* means3D;        /* [P][3]                                            */
+  const float* shs;            /* [P][M][3] or NULL                                 */
+  const float* colors_precomp; /* [P][3] or NULL (V==1 only)                        */
+  const float* opacities;      /* [P]                                               */
+  const float* scales;         /* [P][3] or NULL                                    */
+  float scale_modifier;
+  const float* rotations;      /* [P][4] or NULL                                    */
+  const float* cov3D_precomp;  /* [P][6] or NULL                                    */
+  const float* viewmatrix;     /* [V][16]                                           */
+  const float* projmatrix;     /* [V][16]                                           */
+  const float* cam_pos;        /* [V][3]                                            */
+  float tan_fovx, tan_fovy;
+  float kernel_size;
+  int prefiltered;             /* must be 0                            */
+  int require_coord, require_depth;
+  int debug;                   /* 1: synchronise + check after every stage          */
+  /* outputs, all pre-zeroed by the caller like the reference's torch::full(0) */
+  float* out_color;   /* [V][3][H][W] */
+  float* out_coord;   /* [V][3][H][W] */
+  float* out_mcoord;  /* [V][3][H][W] */
+  float* out_depth;   /* [V][1][H][W] */
+  float* out_mdepth;  /* [V][1][H][W] */
+  float* out_alpha;   /* [V][1][H][W] */
+  float* out_normal;  /* [V][3][H][W] */
+  int* radii;         /* [V][P]       */
+} igs_forward_args;
+
+/* Forward.  *num_rendered receives R = total number of (Gaussian, tile) instances over all views
+ * (the reference's return value, rasterizer_impl.cu:424). */
+int igs_rasterize_forward(const igs_forward_args* args,
+                          igs_alloc_fn geom_alloc, void* geom_user,
+                          igs_alloc_fn binning_alloc, void* binning_user,
+                          igs_alloc_fn image_alloc, void* image_user,
+                          void* stream, int* num_rendered);
+
+typedef struct igs_backward_args {
+  int P, D, M, V, R;
+  int width, height;
+  const float* background;
+  const float* means3D;
+  const float* shs;
+  const float* colors_precomp;
+  const float* scales;
+  float scale_modifier;
+  const float* rotations;
+  const float* cov3D_precomp;
+  const float* viewmatrix;
+  const float* projmatrix;
+  const float* cam_pos;
+  float tan_fovx, tan_fovy;
+  float kernel_size;
+  const int* radii;            /* [V][P] from forward                                */
+  const float* alphas;         /* out_alpha of forward [V][1][H][W]                   */
+  const float* normalmap;      /* out_normal of forward [V][3][H][W]                  */
+  char* geom_buffer;           /* the three forward scratch buffers                   */
+  char* binning_buffer;
+  char* image_buffer;
+  /* cotangents; a NULL pointer means "identically zero" (autograd gave no gradient) */
+  const float* dL_dout_color;  /* [V][3][H][W] */
+  const float* dL_dout_coord;
+  const float* dL_dout_mcoord;
+  const float* dL_dout_depth;
+  const float* dL_dout_mdepth;
+  const float* dL_dout_alpha;
+  const float* dL_dout_normal;
+  /* gradients (every element is written; no pre-zeroing required) */
+  float* dL_dmeans2D;   /* [V][P][3]  (.z = accumulated |grad|)            */
+  float* dL_dcolors;    /* [P][3]     only meaningful with colors_precomp (V==1)       */
+  float* dL_dopacity;   /* [P]                                                         */
+  float* dL_dmeans3D;   /* [P][3]                                                      */
+  float* dL_dcov3D;     /* [P][6]                                                      */
+  float* dL_dsh;        /* [P][M][3] or NULL                                           */
+  float* dL_dscales;    /* [P][3] or NULL                                              */
+  float* dL_drotations; /* [P][4] or NULL                                              */
+  int require_coord, require_depth;
+  int debug;
+} igs_backward_args;
+
+int igs_rasterize_backward(const igs_backward_args* args,
+                           igs_alloc_fn temp_alloc, void* temp_user,
+                           void* stream);
+
+/* present[i] = (view-space z of means3D[i] > 0.2)  — reference in_frustum(), auxiliary.h:155-180 */
+int igs_mark_visible(int P, const float* means3D, const float* viewmatrix,
+                     const float* projmatrix, uint8_t* present, void* stream);
+
+/* Inspection of the opaque forward buffers (parity tests).  Any output pointer may be NULL.
+ *   keys       [R]  u64  (tile << 32) | depth bits, in sorted order      (reference point_list_keys)
+ *   point_list [R]  u32  Gaussian index per sorted instance               (reference point_list)
+ *   ranges     [V*tiles] uint2 {start,end} into the sorted list           (reference ranges)
+ *   n_contrib  [V][2][H*W] u32 last / median contributor                  (reference n_contrib)
+ *   tiles_touched [V][P] u32, depths [V][P] f32, means2D [V][P][2], conic_opacity [V][P][4], rgb [V][P][3]
+ */
+typedef struct igs_decode_out {
+  uint64_t* keys;
+  uint32_t* point_list;
+  uint32_t* ranges;
+  uint32_t* n_contrib;
+  uint32_t* tiles_touched;
+  float* depths;
+  float* means2D;
+  float* conic_opacity;
+  float* rgb;
+  float* cov3D;          /* [P][6] */
+  float* view_points;    /* [V][P][3] */
+  float* camera_planes;  /* [V][P][6] */
+  float* ray_planes;     /* [V][P][2] */
+  float* ts;             /* [V][P]    */
+  float* normals;        /* [V][P][3] */
+} igs_decode_out;
+
+int igs_decode_binning(int P, int V, int R, int width, int height,
+                       const char* geom_buffer, const char* binning_buffer,
+                       const char* image_buffer, const igs_decode_out* out, void* stream);
+
+/* Fused Adam over one parameter group (torch.optim.Adam semantics, no weight decay, no amsgrad):
+ *   m = b1*m + (1-b1)*g ; v = b2*v + (1-b2)*g*g ;
+ *   p -= lr/(1-b1^t) * m / (sqrt(v)/sqrt(1-b2^t) + eps)                                        */
+int igs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
+                  size_t n, float lr, float beta1, float beta2, float eps, int step, void* stream);
+
+const char* igs_last_error(void);
+int igs_abi_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* IGS_RASTER_H_INCLUDED */
