@@ -1,0 +1,465 @@
+#!/usr/bin/env python
+"""bench.py — refine-iteration benchmark (BASELINE.json metric) for the B200-native splat rasterizer.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload C3]
+
+One "step" = one refine iteration on the N3DV-shaped workload (BASELINE.json configs[2], SURVEY §8d
+"C3"): 300k Gaussians SH3, 20 views 1352x1014, activations -> rasterize fwd -> 0.8*L1+0.2*(1-SSIM)
+-> backward -> [NCCL all-reduce of the packed per-Gaussian gradients] -> fused Adam.  With N ranks the
+20 views are sharded v -> rank v mod N (strong scaling: the work of one step is fixed).
+
+Printed JSON line (rank 0):
+  value/ms_per_step  device-timed ms per refine iteration with every input resident in HBM
+  e2e                the same iteration with the Gaussian parameters, cameras and target images of the
+                     step copied from pinned HOST memory inside the timed region and the loss read back
+  fwd_mpix_s         forward-only throughput (the metric's second half)
+  roofline           dominant stage of the step: algorithmic bytes / CUDA-event duration
+  cpu_baseline       the CPU oracle (oracle/raster_oracle.c, a restatement: the reference has no CPU
+                     path) timed on this box's host cores on a bounded sample, N=1 only
+  ref_cuda           (extra) the UNMODIFIED reference CUDA rasterizer (baseline/_ref) on the same views
+                     with the same torch loss, when its build travelled to this box
+`--impl reference` times the CPU oracle port alone (the reference rasterizer is CUDA-only, so its
+"CPU implementation" is the restatement; kind = "port").
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from pathlib import Path
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+METRIC = "refine_iter_ms"
+UNIT = "ms"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="C3")
+    ap.add_argument("--P", type=int, default=0, help="override the number of Gaussians (debug)")
+    ap.add_argument("--views", type=int, default=0, help="override the number of views (debug)")
+    ap.add_argument("--loss", default="auto", choices=["auto", "fused", "torch"])
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-ref-cuda", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--cpu-sample-views", type=int, default=1)
+    return ap.parse_args()
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks sampled DURING the timed region (B200_PROFILING.md recipe)
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.rows = []
+        self.proc = None
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.idx)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.proc = None
+            return
+        self.thread = threading.Thread(target=self._read, daemon=True)
+        self.thread.start()
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append(line.strip())
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons, power = [], [], set(), []
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            f = [x.strip() for x in r.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+                power.append(float(f[3]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(power) if power else None, "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU oracle leg (cpu_baseline and --impl reference)
+# ------------------------------------------------------------------------------------------------
+def cpu_oracle_ms(cfg, views, reps=1):
+    """Times the CPU oracle (oracle/) on `views` views of the workload: forward + backward with the
+    refine loop's colour-only cotangent.  Returns (ms per view, threads used)."""
+    import numpy as np
+    import torch
+    from igs_b200 import scenes
+    sys.path.insert(0, str(ROOT / "oracle"))
+    import oracle_py  # noqa: E402  (ctypes wrapper over oracle/raster_oracle.c; test infrastructure)
+
+    P, W, H, V = cfg["P"], cfg["W"], cfg["H"], cfg["V"]
+    sc = scenes.make_gaussians(P, 0, cfg["log_scale_mean"])
+    cams = scenes.make_cameras(V, W, H, 1)
+    scales, rot, opac = scenes.activated(sc)
+    g = torch.Generator().manual_seed(3)
+    times = []
+    for v in range(views):
+        dcol = torch.randn(3, H, W, generator=g).numpy()
+        t0 = time.perf_counter()
+        for _ in range(reps):
+            fw = oracle_py.forward(sc.xyz.numpy(), scales.numpy(), rot.numpy(), opac.numpy().reshape(-1), sc.sh.numpy(),
+                                   cams.viewmatrix[v].numpy(), cams.projmatrix[v].numpy(), cams.campos[v].numpy(),
+                                   W, H, cams.tanfovx, cams.tanfovy, sh_degree=3)
+            oracle_py.backward(fw, dL_color=dcol)
+        times.append((time.perf_counter() - t0) * 1e3 / reps)
+    return float(np.mean(times)), oracle_py.num_threads()
+
+
+def run_reference_arm(args, cfg, rank):
+    if rank != 0:
+        return 0
+    sample_views = max(1, args.cpu_sample_views)
+    V = cfg["V"]
+    # warm-up + steps, each a bounded sample (sample_views of the V views), scaled to the metric's unit
+    vals = []
+    threads = 1
+    for i in range(args.warmup + args.steps):
+        ms_view, threads = cpu_oracle_ms(cfg, sample_views)
+        if i >= args.warmup:
+            vals.append(ms_view * V)
+    ms = sum(vals) / len(vals)
+    sample = f"{sample_views} of {V} views fwd+bwd (colour cotangent) per step, scaled x{V}/{sample_views}; no loss/Adam"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": ms, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": False, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, cfg),
+        "cpu_baseline": {"value": ms, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": ms, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+        "note": "the reference rasterizer is CUDA-only; this arm is the CPU restatement (oracle/) on host cores",
+    }
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+def workload_config(args, cfg):
+    return {"workload": f"{args.workload}: N3DV-shaped refine iteration, {cfg['P']} Gaussians SH3, {cfg['V']} views "
+                        f"{cfg['W']}x{cfg['H']}, fwd+loss+bwd+Adam, require_coord=require_depth=True",
+            "P": cfg["P"], "views": cfg["V"], "width": cfg["W"], "height": cfg["H"],
+            "parallelism": f"view-sharded x{args.gpus}", "l2": "inputs larger than L2 (working set > 1 GB per step)"}
+
+
+# ------------------------------------------------------------------------------------------------
+def main():
+    args = parse()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    from igs_b200 import scenes
+    cfg = dict(scenes.CONFIGS[args.workload])
+    if args.P:
+        cfg["P"] = args.P
+    if args.views:
+        cfg["V"] = args.views
+
+    if args.impl == "reference":
+        return run_reference_arm(args, cfg, rank)
+
+    import torch
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device — this library has no CPU path (use --impl reference for the CPU oracle)")
+    import torch.distributed as dist
+    from igs_b200 import _C
+    from igs_b200.multiview import MultiViewSettings
+    from igs_b200 import refine
+
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    group = None
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+        group = dist.group.WORLD
+
+    P, W, H, V = cfg["P"], cfg["W"], cfg["H"], cfg["V"]
+    N = W * H
+    loss_impl = args.loss
+    if loss_impl == "auto":
+        loss_impl = "fused" if hasattr(_C, "refine_loss") else "torch"
+
+    # ---- synthetic, seeded inputs, generated on the host ----
+    sc = scenes.make_gaussians(P, 0, cfg["log_scale_mean"])
+    cams = scenes.make_cameras(V, W, H, 1)
+    my_views = refine.shard_views(V, rank, world)
+    Vl = len(my_views)
+    g = torch.Generator().manual_seed(2 + 1000 * rank)
+    gt_host = torch.rand(max(Vl, 1), 3, H, W, generator=g).pin_memory()
+    state = refine.RefineState(sc.xyz, sc.log_scale, sc.rot, sc.opacity_logit, sc.sh, dev)
+    params_host = state.flat.detach().cpu().pin_memory()
+    cam_host = torch.cat([cams.viewmatrix[my_views].reshape(-1), cams.projmatrix[my_views].reshape(-1),
+                          cams.campos[my_views].reshape(-1)]).pin_memory() if Vl else torch.zeros(0).pin_memory()
+    cam_dev = torch.empty_like(cam_host, device=dev)
+    gt_dev = torch.empty(max(Vl, 1), 3, H, W, device=dev)
+    bg = torch.zeros(3, device=dev)
+
+    def settings_from(cam_flat):
+        if Vl == 0:
+            return None
+        vm = cam_flat[:Vl * 16].view(Vl, 4, 4)
+        pm = cam_flat[Vl * 16:Vl * 32].view(Vl, 4, 4)
+        cp = cam_flat[Vl * 32:].view(Vl, 3)
+        return MultiViewSettings(image_height=H, image_width=W, tanfovx=cams.tanfovx, tanfovy=cams.tanfovy,
+                                 kernel_size=0.0, bg=bg, scale_modifier=1.0, viewmatrices=vm, projmatrices=pm,
+                                 sh_degree=3, campos=cp, require_depth=True, require_coord=True, debug=False)
+
+    cam_dev.copy_(cam_host)
+    gt_dev.copy_(gt_host)
+    st = settings_from(cam_dev)
+    gt_local = gt_dev[:Vl]
+
+    def step_resident():
+        return refine.refine_iteration(state, st, gt_local, V, group=group, loss_impl=loss_impl)
+
+    def step_e2e():
+        state.load_flat(params_host)
+        cam_dev.copy_(cam_host, non_blocking=True)
+        gt_dev.copy_(gt_host, non_blocking=True)
+        r = refine.refine_iteration(state, settings_from(cam_dev), gt_dev[:Vl], V, group=group, loss_impl=loss_impl)
+        return float(r.loss.item())  # D2H read of the step's result
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def timed(fn, steps, warmup):
+        for _ in range(warmup):
+            fn()
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        last = None
+        for _ in range(steps):
+            last = fn()
+        e1.record()
+        barrier()
+        ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+        return float(ms.item()) / steps, last
+
+    # ---- (1) device-resident timing with stage timers + clocks ----
+    for _ in range(max(args.warmup, 3)):
+        step_resident()
+    barrier()
+    _C.stage_timing_enable(True)
+    _C.stage_timing_read(True)
+    launches0 = _C.kernel_launches()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    ms_step, last = timed(step_resident, args.steps, 0)
+    clocks = sampler.stop() if rank == 0 else None
+    launches = _C.kernel_launches() - launches0
+    stages = _C.stage_timing_read(True)
+    _C.stage_timing_enable(False)
+    R_local = last.num_rendered
+    loss_val = float(last.loss.item())
+
+    # ---- (2) forward-only throughput ----
+    def fwd_only():
+        with torch.no_grad():
+            return refine.forward_views(state, st) if Vl else None
+    ms_fwd, _ = timed(fwd_only, max(3, args.steps // 2), 2)
+    fwd_mpix = V * N / 1e6 / (ms_fwd / 1e3)
+
+    # ---- (3) end to end: host buffers in, loss out ----
+    e2e = None
+    if not args.no_e2e:
+        ms_e2e, _ = timed(step_e2e, args.steps, max(args.warmup, 3))
+        h2d = params_host.numel() * 4 + cam_host.numel() * 4 + (gt_host[:Vl].numel() * 4 if Vl else 0)
+        e2e = {"value": ms_e2e, "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": 4}
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return 0
+
+    # ---- roofline of the dominant stage ----
+    peaks_file = ROOT / "MEASURED_PEAKS.json"
+    if peaks_file.exists():
+        peak = float(json.loads(peaks_file.read_text())["hbm_gbs"])
+        peak_src = "measured (MEASURED_PEAKS.json hbm_gbs)"
+    else:
+        peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
+    stage_ms = {n: (ms, c) for n, ms, c in stages if c > 0}
+    VP = Vl * P
+    R = R_local
+    # algorithmic bytes per launch of each stage for THIS design
+    alg = {
+        "gauss_setup": P * (28 + 24 + 96),
+        "project": VP * (12 + 4 + 192 + 24 + 96 + 32 + 64 + 4 + 4 + 4 + 1 + 12 + 4),
+        "depth_sort": 5 * VP * (12 + 12) + 5 * VP * 8,
+        "scan_rank": VP * (4 + 4 + 4 + 4) + VP * 8,
+        "emit": VP * (4 + 8 + 32 + 4) + R * 12,
+        "tile_sort": 3 * R * (8 + 8) + 3 * R * 4,
+        "finalize_bins": R * (4 + 4 + 4 + 4),
+        "blend_fwd": R * (4 + 32 + 64) + Vl * N * 88,
+        "blend_bwd": R * (4 + 4 + 32 + 4) + Vl * N * (12 + 4 + 8) + R * 64,
+        "gather_bwd": R * 64 + VP * (32 + 4 + 4 + 8 + 1 + 12 + 64),
+        "finish_bwd": VP * 64 + P * (12 + 192 + 12 + 16 + 12 + 4 + 24 + 192 + 12 + 16),
+        "adam": P * 59 * 4 * 7,
+        "loss": Vl * N * 3 * 4 * 3,
+    }
+    top = max(stage_ms.items(), key=lambda kv: kv[1][0])[0] if stage_ms else None
+    roofline = None
+    if top:
+        tot_ms, cnt = stage_ms[top]
+        per_launch_ms = tot_ms / cnt
+        achieved = alg[top] / 1e9 / (per_launch_ms / 1e3)
+        traffic = None
+        tf = ROOT / "profiles" / "traffic.json"   # per-launch dram bytes from an `ncu --set full` capture, if committed
+        if tf.exists():
+            traffic = json.loads(tf.read_text()).get(top)
+        roofline = {"bound": "hbm", "kernel": top, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                    "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                    "algorithmic_bytes_per_launch": alg[top], "ms_per_launch": per_launch_ms,
+                    "note": "blend kernels are FP32/MUFU/shared-memory bound, not HBM bound (DESIGN.md); "
+                            "HBM fraction is reported because the contract asks for hbm|tensor"}
+    stage_report = {n: {"ms_per_step": ms / args.steps, "launches_per_step": c / args.steps,
+                        "alg_GBps": (alg[n] * (c / args.steps)) / 1e9 / (ms / args.steps / 1e3) if ms > 0 else None}
+                    for n, (ms, c) in stage_ms.items()}
+
+    # ---- CPU baseline (bounded sample) ----
+    cpu_baseline = None
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            ms_view, threads = cpu_oracle_ms(cfg, max(1, args.cpu_sample_views))
+            cpu_baseline = {"value": ms_view * V, "unit": UNIT, "cores": threads, "kind": "port",
+                            "sample": f"{max(1, args.cpu_sample_views)} of {V} views fwd+bwd on the CPU oracle "
+                                      f"(oracle/raster_oracle.c), scaled x{V}; no loss/Adam"}
+        except Exception as ex:  # the oracle is a checker; its absence must not hide the GPU number
+            cpu_baseline = {"value": None, "unit": UNIT, "cores": 0, "kind": "port", "sample": f"unavailable: {ex}"}
+
+    # ---- reference CUDA rasterizer on the same views (extra evidence, not the `reference` arm) ----
+    ref_cuda = None
+    if world == 1 and not args.no_ref_cuda:
+        try:
+            ref_cuda = time_reference_cuda(cfg, cams, sc, gt_dev, dev, loss_impl="torch")
+        except Exception as ex:
+            ref_cuda = {"unavailable": str(ex)[:200]}
+
+    line = {
+        "metric": METRIC, "value": ms_step, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": max(args.warmup, 3),
+        "ms_per_step": ms_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
+        "data": "synthetic", "config": workload_config(args, cfg), "e2e": e2e, "gpu_launches": int(launches),
+        "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
+        "fwd_mpix_s": fwd_mpix, "fwd_ms": ms_fwd, "loss": loss_val, "loss_impl": loss_impl,
+        "num_rendered_rank0": int(R_local), "stages": stage_report, "ref_cuda": ref_cuda,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def time_reference_cuda(cfg, cams, sc, gt_dev, dev, loss_impl="torch", steps=3):
+    """The unmodified reference rasterizer (baseline/_ref) on the same V views: per view
+    forward -> same loss -> backward, gradients accumulated over the views, one torch Adam step
+    (our schedule; the reference's own schedule is one Adam step per view)."""
+    import torch
+    import torch.nn.functional as F
+    sys.path.insert(0, str(ROOT / "tests"))
+    import ref_loader
+    from igs_b200 import refine
+    ref = ref_loader.load_reference()
+    if ref is None:
+        return {"unavailable": "baseline/_ref not built on this box"}
+    P, W, H, V = cfg["P"], cfg["W"], cfg["H"], cfg["V"]
+    params = [sc.xyz.to(dev).requires_grad_(True), sc.sh.to(dev).requires_grad_(True),
+              sc.log_scale.to(dev).requires_grad_(True), sc.rot.to(dev).requires_grad_(True),
+              sc.opacity_logit.to(dev).requires_grad_(True)]
+    lrs = refine.DEFAULT_LRS
+    opt = torch.optim.Adam([{"params": [params[0]], "lr": lrs["xyz"]}, {"params": [params[1]], "lr": lrs["shs"]},
+                            {"params": [params[2]], "lr": lrs["scaling"]}, {"params": [params[3]], "lr": lrs["rotation"]},
+                            {"params": [params[4]], "lr": lrs["opacity"]}], lr=0.0, eps=1e-15)
+    bg = torch.zeros(3, device=dev)
+    vms = cams.viewmatrix.to(dev)
+    pms = cams.projmatrix.to(dev)
+    cps = cams.campos.to(dev)
+
+    def one_step(fwd_only=False):
+        tot = 0.0
+        for v in range(V):
+            xyz, sh, ls, rot, ol = params
+            stt = ref.GaussianRasterizationSettings(
+                image_height=H, image_width=W, tanfovx=cams.tanfovx, tanfovy=cams.tanfovy, kernel_size=0.0, bg=bg,
+                scale_modifier=1.0, viewmatrix=vms[v], projmatrix=pms[v], sh_degree=3, campos=cps[v], prefiltered=False,
+                require_depth=True, require_coord=True, debug=False)
+            m2 = torch.zeros_like(xyz, requires_grad=True)
+            outs = ref.GaussianRasterizer(raster_settings=stt)(
+                means3D=xyz, means2D=m2, opacities=torch.sigmoid(ol), shs=sh, scales=torch.exp(ls), rotations=F.normalize(rot))
+            if fwd_only:
+                continue
+            loss = refine.refine_loss_torch(outs[0].unsqueeze(0), gt_dev[v:v + 1]).sum() / V
+            loss.backward()
+            tot = loss
+        if not fwd_only:
+            opt.step()
+            opt.zero_grad(set_to_none=True)
+        return tot
+
+    for _ in range(2):
+        one_step()
+    torch.cuda.synchronize()
+    e0, e1, e2 = (torch.cuda.Event(enable_timing=True) for _ in range(3))
+    e0.record()
+    for _ in range(steps):
+        one_step()
+    e1.record()
+    with torch.no_grad():
+        for _ in range(steps):
+            one_step(fwd_only=True)
+    e2.record()
+    torch.cuda.synchronize()
+    ms = e0.elapsed_time(e1) / steps
+    ms_f = e1.elapsed_time(e2) / steps
+    return {"ms_per_step": ms, "fwd_ms": ms_f, "fwd_mpix_s": V * W * H / 1e6 / (ms_f / 1e3), "steps": steps,
+            "schedule": "V views accumulated, one torch Adam step; torch L1+SSIM loss; reference rasterizer sm_100a build"}
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -4,18 +4,68 @@
 #include "../../include/igs_raster.h"
 #include "common.cuh"
 #include "kernels.cuh"
+#include <atomic>
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
+#include <vector>
 
 namespace igs {
 
 static thread_local char g_err[512] = "";
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 void set_error(const char* fmt, ...) {
   va_list ap;
   va_start(ap, fmt);
   vsnprintf(g_err, sizeof(g_err), fmt, ap);
   va_end(ap);
+}
+
+// ---- per-stage device timing (bench.py's roofline evidence; off by default) ----
+// When enabled, an event pair is recorded on the launching stream around every stage; durations are
+// resolved lazily in igs_stage_timing_read() so that no synchronisation is added to the timed path.
+static const char* const kStageNames[IGS_NUM_STAGES] = {
+    "gauss_setup", "project", "depth_sort", "scan_rank", "emit", "tile_sort", "finalize_bins", "blend_fwd",
+    "blend_bwd", "gather_bwd", "finish_bwd", "adam", "loss"};
+struct StageTimer {
+  std::mutex mu;
+  bool on = false;
+  std::vector<cudaEvent_t> pool;
+  struct Pending { int stage; cudaEvent_t a, b; };
+  std::vector<Pending> pending;
+  double ms[IGS_NUM_STAGES] = {0};
+  unsigned long long count[IGS_NUM_STAGES] = {0};
+  cudaEvent_t get() {
+    if (!pool.empty()) { cudaEvent_t e = pool.back(); pool.pop_back(); return e; }
+    cudaEvent_t e; cudaEventCreate(&e); return e;
+  }
+  void drain() {
+    for (auto& q : pending) {
+      float t = 0.f;
+      if (cudaEventSynchronize(q.b) == cudaSuccess && cudaEventElapsedTime(&t, q.a, q.b) == cudaSuccess) {
+        ms[q.stage] += t; count[q.stage]++;
+      }
+      pool.push_back(q.a); pool.push_back(q.b);
+    }
+    pending.clear();
+  }
+};
+static StageTimer g_timer;
+StageScope::StageScope(int stage, cudaStream_t s) : stage_(stage), s_(s), a_(nullptr) {
+  if (!g_timer.on) return;
+  std::lock_guard<std::mutex> lk(g_timer.mu);
+  a_ = g_timer.get();
+  cudaEventRecord((cudaEvent_t)a_, s_);
+}
+StageScope::~StageScope() {
+  if (!a_) return;
+  std::lock_guard<std::mutex> lk(g_timer.mu);
+  cudaEvent_t b = g_timer.get();
+  cudaEventRecord(b, s_);
+  g_timer.pending.push_back({stage_, (cudaEvent_t)a_, b});
+  if (g_timer.pending.size() > 4096) g_timer.drain();
 }
 
 // ---- small kernels local to this file ----
@@ -70,6 +120,22 @@ extern "C" {
 
 const char* igs_last_error(void) { return igs::g_err; }
 int igs_abi_version(void) { return IGS_RASTER_ABI_VERSION; }
+void igs_stage_timing_enable(int on) {
+  std::lock_guard<std::mutex> lk(igs::g_timer.mu);
+  igs::g_timer.on = on != 0;
+}
+int igs_stage_timing_read(double* ms, unsigned long long* counts, int n, int reset) {
+  std::lock_guard<std::mutex> lk(igs::g_timer.mu);
+  igs::g_timer.drain();
+  for (int i = 0; i < n && i < IGS_NUM_STAGES; i++) {
+    if (ms) ms[i] = igs::g_timer.ms[i];
+    if (counts) counts[i] = igs::g_timer.count[i];
+  }
+  if (reset) for (int i = 0; i < IGS_NUM_STAGES; i++) { igs::g_timer.ms[i] = 0; igs::g_timer.count[i] = 0; }
+  return IGS_NUM_STAGES;
+}
+const char* igs_stage_name(int i) { return (i >= 0 && i < IGS_NUM_STAGES) ? igs::kStageNames[i] : ""; }
+unsigned long long igs_kernel_launches(void) { return igs::g_launches.load(std::memory_order_relaxed); }
 
 int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, void* geom_user,
                           igs_alloc_fn bin_alloc, void* bin_user, igs_alloc_fn img_alloc, void* img_user,
@@ -105,8 +171,10 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   if (!iptr) { set_error("image allocator returned NULL for %zu bytes", isz.bytes); return IGS_ERR_ALLOC; }
   ImgBuf I = carve_img(iptr, V, N, tiles);
 
+  count_launch();
   pack_cameras_kernel<<<V, 64, 0, s>>>(V, a->viewmatrix, a->projmatrix, a->cam_pos, G.cams);
-  launch_gauss_setup(P, a->scales, a->scale_modifier, a->rotations, a->cov3D_precomp, G.cov3D, G.eig, s);
+  { StageScope st(IGS_STAGE_GAUSS_SETUP, s);
+  launch_gauss_setup(P, a->scales, a->scale_modifier, a->rotations, a->cov3D_precomp, G.cov3D, G.eig, s); }
   if (int e = debug_sync(dbg, s, "gauss_setup")) return e;
 
   ProjectParams pp;
@@ -114,22 +182,26 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   pp.tan_fovx = a->tan_fovx; pp.tan_fovy = a->tan_fovy; pp.focal_x = focal_x; pp.focal_y = focal_y;
   pp.kernel_size = a->kernel_size;
   pp.means3D = a->means3D; pp.opacities = a->opacities; pp.shs = a->shs; pp.colors_precomp = a->colors_precomp;
-  launch_project(pp, G, a->radii, s);
+  { StageScope st(IGS_STAGE_PROJECT, s); launch_project(pp, G, a->radii, s); }
   if (int e = debug_sync(dbg, s, "project")) return e;
 
   // ---- sort A: (view, depth) ----
-  int cur = radix_sort_pairs<uint64_t>(G.skey, G.sval, VP, 32 + (V > 1 ? bits_for((uint64_t)V) : 0), G.hist, nullptr, s);
+  int cur;
+  { StageScope st(IGS_STAGE_DEPTH_SORT, s);
+    cur = radix_sort_pairs<uint64_t>(G.skey, G.sval, VP, 32 + (V > 1 ? bits_for((uint64_t)V) : 0), G.hist, nullptr, s); }
   if (int e = debug_sync(dbg, s, "depth sort")) return e;
   const uint32_t* sorted_gid = G.sval[cur];
-  launch_gather_rank(VP, sorted_gid, G.tiles, G.inst_off, G.rank, s);
   uint32_t* d_total = G.scan_tmp + scan_blocks(VP + 1);
-  launch_exclusive_scan(G.inst_off, G.inst_off, VP + 1, G.scan_tmp, d_total, s);
+  { StageScope st(IGS_STAGE_SCAN_RANK, s);
+    launch_gather_rank(VP, sorted_gid, G.tiles, G.inst_off, G.rank, s);
+    launch_exclusive_scan(G.inst_off, G.inst_off, VP + 1, G.scan_tmp, d_total, s); }
 
   Header hv;
   memset(&hv, 0, sizeof(hv));
   hv.magic = IGS_MAGIC; hv.P = P; hv.V = V; hv.N = (uint32_t)N; hv.tiles_x = tiles_x; hv.tiles_y = tiles_y;
   hv.flags = (a->require_coord ? 1u : 0u) | (a->require_depth ? 2u : 0u) | (a->scales ? 8u : 0u) | (a->shs ? 16u : 0u) |
              ((uint32_t)cur << 8);
+  count_launch();
   write_header_kernel<<<1, 1, 0, s>>>(G.hdr, hv, d_total);
 
   // ---- the one host sync: instance count (reference rasterizer_impl.cu:354) ----
@@ -146,17 +218,21 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   IGS_CUDA_CHECK(cudaMemsetAsync(I.ranges, 0, sizeof(uint2) * V * tiles, s));
   int bcur = 0;
   if (R > 0) {
-    launch_emit_instances(VP, (uint32_t)P, tiles_x, tiles_y, sorted_gid, G.inst_off, G.head, G.radii, B.tkey[0],
-                          B.tval[0], B.inst_gid, s);
+    { StageScope st(IGS_STAGE_EMIT, s);
+      launch_emit_instances(VP, (uint32_t)P, tiles_x, tiles_y, sorted_gid, G.inst_off, G.head, G.radii, B.tkey[0],
+                            B.tval[0], B.inst_gid, s); }
     if (int e = debug_sync(dbg, s, "emit")) return e;
-    bcur = radix_sort_pairs<uint32_t>(B.tkey, B.tval, R, bits_for((uint64_t)V * tiles), B.hist, nullptr, s);
+    { StageScope st(IGS_STAGE_TILE_SORT, s);
+      bcur = radix_sort_pairs<uint32_t>(B.tkey, B.tval, R, bits_for((uint64_t)V * tiles), B.hist, nullptr, s); }
     if (int e = debug_sync(dbg, s, "tile sort")) return e;
-    launch_finalize_bins(R, B.tkey[bcur], B.tval[bcur], B.inst_gid, B.point_list, I.ranges, s);
+    { StageScope st(IGS_STAGE_FINALIZE, s);
+      launch_finalize_bins(R, B.tkey[bcur], B.tval[bcur], B.inst_gid, B.point_list, I.ranges, s); }
     if (int e = debug_sync(dbg, s, "finalize bins")) return e;
   }
   // remember which ping-pong buffer holds the sorted instances (bit 16 of flags)
   {
     hv.flags |= ((uint32_t)bcur << 16);
+    count_launch();
     write_header_kernel<<<1, 1, 0, s>>>(G.hdr, hv, d_total);
   }
 
@@ -167,7 +243,7 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   bp.out_mdepth = a->out_mdepth; bp.out_alpha = a->out_alpha; bp.out_normal = a->out_normal;
   bp.n_contrib = I.n_contrib; bp.accum_coord = I.accum_coord; bp.accum_depth = I.accum_depth;
   bp.normal_length = I.normal_length;
-  launch_blend_fwd(bp, V, a->require_coord != 0, a->require_depth != 0, s);
+  { StageScope st(IGS_STAGE_BLEND_FWD, s); launch_blend_fwd(bp, V, a->require_coord != 0, a->require_depth != 0, s); }
   if (int e = debug_sync(dbg, s, "blend forward")) return e;
   IGS_CUDA_CHECK(cudaGetLastError());
   if (num_rendered) *num_rendered = (int)R;
@@ -223,7 +299,7 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
     bp.dL_color = a->dL_dout_color; bp.dL_coord = a->dL_dout_coord; bp.dL_mcoord = a->dL_dout_mcoord;
     bp.dL_depth = a->dL_dout_depth; bp.dL_mdepth = a->dL_dout_mdepth; bp.dL_alpha = a->dL_dout_alpha;
     bp.dL_normal = a->dL_dout_normal; bp.grec = grec;
-    launch_blend_bwd(bp, V, coord, depth, geograd, s);
+    { StageScope st(IGS_STAGE_BLEND_BWD, s); launch_blend_bwd(bp, V, coord, depth, geograd, s); }
     if (int e = debug_sync(dbg, s, "blend backward")) return e;
   }
 
@@ -233,7 +309,7 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   gp.means3D = a->means3D; gp.cams = G.cams; gp.cov3D = G.cov3D; gp.eig = G.eig; gp.head = G.head; gp.radii = G.radii;
   gp.tiles = G.tiles; gp.rank = G.rank; gp.inst_off = G.inst_off; gp.clamped = G.clamped; gp.grec = grec;
   gp.dL_dmeans2D = a->dL_dmeans2D; gp.partial = partial;
-  launch_gather_bwd(gp, s);
+  { StageScope st(IGS_STAGE_GATHER_BWD, s); launch_gather_bwd(gp, s); }
   if (int e = debug_sync(dbg, s, "gather backward")) return e;
 
   FinishBwdParams fp;
@@ -242,7 +318,7 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   fp.partial = partial; fp.dL_dmeans3D = a->dL_dmeans3D; fp.dL_dcov3D = a->dL_dcov3D; fp.dL_dopacity = a->dL_dopacity;
   fp.dL_dcolors = a->dL_dcolors; fp.dL_dsh = a->shs ? a->dL_dsh : nullptr; fp.dL_dscales = a->dL_dscales;
   fp.dL_drotations = a->dL_drotations;
-  launch_finish_bwd(fp, s);
+  { StageScope st(IGS_STAGE_FINISH_BWD, s); launch_finish_bwd(fp, s); }
   if (int e = debug_sync(dbg, s, "finish backward")) return e;
   IGS_CUDA_CHECK(cudaGetLastError());
   return IGS_OK;
@@ -306,8 +382,12 @@ int igs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
   float inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
   size_t nb = (n + 255) / 256;
   if (nb > 148 * 16) nb = 148 * 16;
-  adam_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, beta1, beta2, eps,
-                                                                step_size, inv_sqrt_bc2);
+  count_launch();
+  {
+    StageScope st(IGS_STAGE_ADAM, (cudaStream_t)stream);
+    adam_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, beta1, beta2, eps,
+                                                                  step_size, inv_sqrt_bc2);
+  }
   IGS_CUDA_CHECK(cudaGetLastError());
   return IGS_OK;
 }

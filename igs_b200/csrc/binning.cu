@@ -98,6 +98,7 @@ void launch_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint32_t
                            uint32_t* total, cudaStream_t s) {
   if (n == 0) return;
   unsigned nb = (unsigned)scan_blocks(n);
+  count_launch(2);
   scan_block_sums_kernel<<<nb, SCAN_THREADS, 0, s>>>(in, n, block_sums);
   scan_apply_kernel<<<nb, SCAN_THREADS, 0, s>>>(in, n, block_sums, out, total);
 }
@@ -205,6 +206,7 @@ int radix_sort_pairs(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint3
   for (int shift = 0; shift < end_bit; shift += 8) {
     int bits = end_bit - shift < 8 ? end_bit - shift : 8;
     uint32_t mask = (1u << bits) - 1u;
+    count_launch(2);
     radix_hist_kernel<K><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], n, shift, mask, hist, nb);
     // in-place exclusive scan over the bin-major histogram
     launch_exclusive_scan(hist, hist, (size_t)256 * nb, hist + (size_t)256 * nb, nullptr, s);
@@ -235,6 +237,7 @@ gather_rank_kernel(size_t VP, const uint32_t* __restrict__ sorted_gid, const uin
 void launch_gather_rank(size_t VP, const uint32_t* sorted_gid, const uint32_t* tiles, uint32_t* tiles_sorted,
                         uint32_t* rank, cudaStream_t s) {
   unsigned nb = (unsigned)((VP + 1 + 255) / 256);
+  count_launch();
   gather_rank_kernel<<<nb, 256, 0, s>>>(VP, sorted_gid, tiles, tiles_sorted, rank);
 }
 
@@ -281,6 +284,7 @@ void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, cons
                            uint32_t* tval, uint32_t* inst_gid, cudaStream_t s) {
   if (VP == 0) return;
   unsigned nb = (unsigned)((VP + 255) / 256);
+  count_launch();
   emit_instances_kernel<<<nb, 256, 0, s>>>(VP, P, tiles_x, tiles_y, sorted_gid, inst_off, head, radii, tkey, tval,
                                            inst_gid);
 }
@@ -311,6 +315,7 @@ finalize_bins_kernel(uint32_t R, const uint32_t* __restrict__ tkey, const uint32
 void launch_finalize_bins(uint32_t R, const uint32_t* tkey, const uint32_t* point_e, const uint32_t* inst_gid,
                           uint32_t* point_list, uint2* ranges, cudaStream_t s) {
   if (R == 0) return;
+  count_launch();
   finalize_bins_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, tkey, point_e, inst_gid, point_list, ranges);
 }
 
@@ -329,6 +334,7 @@ void launch_decode_keys(uint32_t R, uint32_t tiles_per_view, uint32_t P, const u
                         const uint32_t* point_list, const float* depth, uint64_t* keys, uint32_t* plist_local,
                         cudaStream_t s) {
   if (R == 0) return;
+  count_launch();
   decode_keys_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, tiles_per_view, P, tkey, point_list, depth, keys, plist_local);
 }
 

@@ -353,6 +353,7 @@ int blend_bwd_record_floats(bool geograd) { return geograd ? 32 : 16; }
 void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s) {
   int nblocks = V * p.tiles_x * p.tiles_y;
   if (nblocks <= 0) return;
+  count_launch();
   if (!geograd || (!coord && !depth)) {
     blend_bwd_kernel<false, false, false, false><<<nblocks, 256, 0, s>>>(p);
   } else if (coord && depth) {

@@ -235,6 +235,7 @@ blend_fwd_kernel(BlendFwdParams p) {
 void launch_blend_fwd(const BlendFwdParams& p, int V, bool coord, bool depth, cudaStream_t s) {
   int nblocks = V * p.tiles_x * p.tiles_y;
   if (nblocks <= 0) return;
+  count_launch();
   if (coord && depth) blend_fwd_kernel<true, true, true><<<nblocks, 256, 0, s>>>(p);
   else if (coord && !depth) blend_fwd_kernel<true, false, true><<<nblocks, 256, 0, s>>>(p);
   else if (!coord && depth) blend_fwd_kernel<false, true, true><<<nblocks, 256, 0, s>>>(p);

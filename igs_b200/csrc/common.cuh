@@ -225,7 +225,23 @@ __device__ __forceinline__ uint32_t lane_id() { return threadIdx.x & 31; }
 // error plumbing shared by the host-side translation units
 namespace igs {
 void set_error(const char* fmt, ...);
+void count_launch(int n = 1);  // bumps the counter behind igs_kernel_launches()
+// RAII event pair around one stage (no-op unless igs_stage_timing_enable(1) was called)
+class StageScope {
+ public:
+  StageScope(int stage, cudaStream_t s);
+  ~StageScope();
+ private:
+  int stage_;
+  cudaStream_t s_;
+  void* a_;
+};
 }
+enum {
+  IGS_STAGE_GAUSS_SETUP = 0, IGS_STAGE_PROJECT, IGS_STAGE_DEPTH_SORT, IGS_STAGE_SCAN_RANK, IGS_STAGE_EMIT,
+  IGS_STAGE_TILE_SORT, IGS_STAGE_FINALIZE, IGS_STAGE_BLEND_FWD, IGS_STAGE_BLEND_BWD, IGS_STAGE_GATHER_BWD,
+  IGS_STAGE_FINISH_BWD, IGS_STAGE_ADAM, IGS_STAGE_LOSS, IGS_NUM_STAGES
+};
 #define IGS_CUDA_CHECK(expr)                                                      \
   do {                                                                            \
     cudaError_t _e = (expr);                                                      \

@@ -348,18 +348,21 @@ __global__ void mark_visible_kernel(int P, const float* __restrict__ means3D, co
 void launch_gauss_setup(int P, const float* scales, float mod, const float* rotations,
                         const float* cov3D_precomp, float* cov3D_out, GaussEig* eig, cudaStream_t s) {
   if (P <= 0) return;
+  count_launch();
   gauss_setup_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, scales, mod, rotations, cov3D_precomp, cov3D_out, eig);
 }
 
 void launch_project(const ProjectParams& p, const GeomBuf& g, int* radii_out, cudaStream_t s) {
   if (p.P <= 0) return;
   dim3 grid((p.P + 255) / 256, p.V);
+  count_launch();
   project_kernel<<<grid, 256, 0, s>>>(p, g.cams, g.cov3D, g.eig, g.head, g.tail, g.depth, g.radii, radii_out,
                                       g.tiles, g.clamped, g.skey[0], g.sval[0]);
 }
 
 void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t* present, cudaStream_t s) {
   if (P <= 0) return;
+  count_launch();
   mark_visible_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, means3D, view, present);
 }
 

@@ -486,6 +486,7 @@ finish_bwd_kernel(FinishBwdParams p) {
 void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s) {
   if (p.P <= 0) return;
   dim3 grid((p.P + 127) / 128, p.V);
+  count_launch();
   gather_bwd_kernel<<<grid, 128, 0, s>>>(p);
 }
 
@@ -493,6 +494,7 @@ void launch_finish_bwd(const FinishBwdParams& p, cudaStream_t s) {
   if (p.P <= 0) return;
   int nb = (p.P + 127) / 128;
   int need = p.shs ? p.M : 1;
+  count_launch();
   if (need <= 1) finish_bwd_kernel<1><<<nb, 128, 0, s>>>(p);
   else if (need <= 4) finish_bwd_kernel<4><<<nb, 128, 0, s>>>(p);
   else if (need <= 9) finish_bwd_kernel<9><<<nb, 128, 0, s>>>(p);

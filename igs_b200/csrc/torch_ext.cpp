@@ -8,6 +8,7 @@
 #include <torch/extension.h>
 #include <ATen/cuda/CUDAContext.h>
 #include <c10/cuda/CUDAGuard.h>
+#include <string>
 #include <tuple>
 #include <vector>
 #include "../../include/igs_raster.h"
@@ -318,4 +319,13 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("decode_buffers", &DecodeBuffers);
   m.def("adam_step", &AdamStep);
   m.def("abi_version", []() { return igs_abi_version(); });
+  m.def("stage_timing_enable", [](bool on) { igs_stage_timing_enable(on ? 1 : 0); });
+  m.def("stage_timing_read", [](bool reset) {
+    double ms[64]; unsigned long long cnt[64];
+    int n = igs_stage_timing_read(ms, cnt, 64, reset ? 1 : 0);
+    std::vector<std::tuple<std::string, double, int64_t>> out;
+    for (int i = 0; i < n; i++) out.emplace_back(std::string(igs_stage_name(i)), ms[i], (int64_t)cnt[i]);
+    return out;
+  });
+  m.def("kernel_launches", []() { return (int64_t)igs_kernel_launches(); });
 }

@@ -1,0 +1,202 @@
+"""One refine iteration of IGS's per-key-frame loop on the B200-native rasterizer.
+
+Reference: infer_batch.py:279-324 (render -> 0.8*L1 + 0.2*(1-SSIM) -> backward -> Adam(eps=1e-15)),
+igs/models/gaussian_model.py:89-127 (activations) and :265-348 (parameter groups / learning rates),
+igs/utils/loss_utils.py:16-62 (l1_loss, ssim).  The reference renders ONE view per Adam step; the
+schedule here is BASELINE.json's: V views per step, sharded by view over the ranks of a process
+group, per-Gaussian gradients summed with one NCCL all-reduce over a packed [P*59] buffer, then an
+identical fused Adam step on every rank.  `views_per_step=1` on one rank is the
+reference's schedule.
+
+The loss can run through torch (`loss_impl="torch"`, a restatement of loss_utils.py with grouped
+conv2d) or through the hand-written fused L1+SSIM kernel (`loss_impl="fused"`, csrc/loss.cu) that
+writes dL/dcolor directly; both give the same value/gradient within fp32 rounding (tests).
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, NamedTuple, Optional
+
+import torch
+import torch.nn.functional as F
+
+from . import _C
+from .multiview import MultiViewSettings, rasterize_views
+
+# configs/demo.yaml:66-71 `training_lr`
+DEFAULT_LRS = dict(xyz=0.0016, shs=0.0025, opacity=0.05, scaling=0.005, rotation=0.01)
+# packing order of the [P*59] gradient / parameter record
+GROUPS = (("xyz", 3), ("rotation", 4), ("shs", 48), ("opacity", 1), ("scaling", 3))
+FLOATS_PER_GAUSSIAN = sum(n for _, n in GROUPS)  # 59
+
+
+class RefineState:
+    """Refine parameters (pre-activation, like GaussianModel._xyz/_shs/_opacity/_scaling/_rotation),
+    Adam moments and the packed gradient buffer, all resident on one device."""
+
+    def __init__(self, xyz, log_scale, rot, opacity_logit, sh, device, lrs: Optional[Dict[str, float]] = None):
+        P = xyz.shape[0]
+        self.P = P
+        self.device = torch.device(device)
+        self.lrs = dict(DEFAULT_LRS if lrs is None else lrs)
+        src = dict(xyz=xyz, rotation=rot, shs=sh.reshape(P, 48), opacity=opacity_logit.reshape(P, 1), scaling=log_scale)
+        # one flat buffer each for params / grads / exp_avg / exp_avg_sq, grouped (not interleaved)
+        n = P * FLOATS_PER_GAUSSIAN
+        self.flat = torch.empty(n, device=self.device, dtype=torch.float32)
+        self.grad = torch.zeros(n, device=self.device, dtype=torch.float32)
+        self.exp_avg = torch.zeros(n, device=self.device, dtype=torch.float32)
+        self.exp_avg_sq = torch.zeros(n, device=self.device, dtype=torch.float32)
+        self.slices = {}
+        off = 0
+        for name, k in GROUPS:
+            self.slices[name] = (off, off + P * k, k)
+            self.flat[off:off + P * k].copy_(src[name].reshape(-1).to(self.device, non_blocking=True))
+            off += P * k
+        self.step = 0
+
+    def view(self, buf: torch.Tensor, name: str) -> torch.Tensor:
+        a, b, k = self.slices[name]
+        t = buf[a:b]
+        return t.view(self.P, 16, 3) if name == "shs" else t.view(self.P, k)
+
+    def param(self, name: str) -> torch.Tensor:
+        return self.view(self.flat, name)
+
+    def load_flat(self, host_flat: torch.Tensor) -> None:
+        """H2D copy of all parameters from a (pinned) host buffer laid out like `self.flat`."""
+        self.flat.copy_(host_flat, non_blocking=True)
+
+    def adam_step(self) -> None:
+        """torch.optim.Adam(lr per group, betas=(0.9,0.999), eps=1e-15) — gaussian_model.py:348 — as one
+        fused kernel launch per parameter group (igs_adam_step)."""
+        self.step += 1
+        for name, _ in GROUPS:
+            a, b, _k = self.slices[name]
+            _C.adam_step(self.flat[a:b], self.grad[a:b], self.exp_avg[a:b], self.exp_avg_sq[a:b],
+                         float(self.lrs[name]), 0.9, 0.999, 1e-15, self.step)
+
+
+# ------------------------------------------------------------------------------------------------
+# loss (reference igs/utils/loss_utils.py:16-62), torch restatement
+# ------------------------------------------------------------------------------------------------
+_WINDOWS: Dict[tuple, torch.Tensor] = {}
+
+
+def _window(channel: int, device, dtype) -> torch.Tensor:
+    key = (channel, str(device), dtype)
+    if key not in _WINDOWS:
+        g = torch.tensor([math.exp(-(x - 11 // 2) ** 2 / float(2 * 1.5 ** 2)) for x in range(11)])
+        g = (g / g.sum()).unsqueeze(1)
+        w2 = g.mm(g.t()).float().unsqueeze(0).unsqueeze(0)
+        _WINDOWS[key] = w2.expand(channel, 1, 11, 11).contiguous().to(device=device, dtype=dtype)
+    return _WINDOWS[key]
+
+
+def ssim_map_torch(img1: torch.Tensor, img2: torch.Tensor) -> torch.Tensor:
+    """[V,3,H,W] x [V,3,H,W] -> SSIM map [V,3,H,W] (loss_utils.py:43-57)."""
+    ch = img1.shape[-3]
+    w = _window(ch, img1.device, img1.dtype)
+    mu1 = F.conv2d(img1, w, padding=5, groups=ch)
+    mu2 = F.conv2d(img2, w, padding=5, groups=ch)
+    mu1_sq, mu2_sq, mu1_mu2 = mu1.pow(2), mu2.pow(2), mu1 * mu2
+    s1 = F.conv2d(img1 * img1, w, padding=5, groups=ch) - mu1_sq
+    s2 = F.conv2d(img2 * img2, w, padding=5, groups=ch) - mu2_sq
+    s12 = F.conv2d(img1 * img2, w, padding=5, groups=ch) - mu1_mu2
+    C1, C2 = 0.01 ** 2, 0.03 ** 2
+    return ((2 * mu1_mu2 + C1) * (2 * s12 + C2)) / ((mu1_sq + mu2_sq + C1) * (s1 + s2 + C2))
+
+
+def refine_loss_torch(pred: torch.Tensor, gt: torch.Tensor, lambda_l1: float = 0.8) -> torch.Tensor:
+    """Per-view loss [V]: lambda*L1 + (1-lambda)*(1-SSIM) (infer_batch.py:302-305)."""
+    l1 = (pred - gt).abs().mean(dim=(1, 2, 3))
+    ss = ssim_map_torch(pred, gt).mean(dim=(1, 2, 3))
+    return lambda_l1 * l1 + (1.0 - lambda_l1) * (1.0 - ss)
+
+
+class _FusedLoss(torch.autograd.Function):
+    """Sum over views of the per-view refine loss, value and dL/dpred from csrc/loss.cu."""
+
+    @staticmethod
+    def forward(ctx, pred, gt, lambda_l1):
+        loss_sum, dpred = _C.refine_loss(pred, gt, float(lambda_l1))
+        ctx.save_for_backward(dpred)
+        return loss_sum
+
+    @staticmethod
+    def backward(ctx, g):
+        (dpred,) = ctx.saved_tensors
+        return dpred * g, None, None
+
+
+def refine_loss_sum(pred, gt, lambda_l1=0.8, impl="fused"):
+    if impl == "fused":
+        return _FusedLoss.apply(pred.contiguous(), gt.contiguous(), lambda_l1)
+    return refine_loss_torch(pred, gt, lambda_l1).sum()
+
+
+# ------------------------------------------------------------------------------------------------
+# the iteration
+# ------------------------------------------------------------------------------------------------
+class IterationResult(NamedTuple):
+    loss: torch.Tensor           # scalar, mean over ALL views of the step (after all-reduce)
+    num_rendered: int
+    radii: torch.Tensor          # [V_local,P]
+    grad_means2D: Optional[torch.Tensor]  # [V_local,P,3] screen-space grads (densification statistics)
+
+
+def forward_views(state: RefineState, settings: MultiViewSettings):
+    """Activations (gaussian_model.py:89-127) + batched rasterization; returns the 8 output maps."""
+    xyz = state.param("xyz")
+    scales = torch.exp(state.param("scaling"))
+    rot = F.normalize(state.param("rotation"))
+    opac = torch.sigmoid(state.param("opacity"))
+    return rasterize_views(xyz, state.param("shs"), opac, scales, rot, settings)
+
+
+def refine_iteration(state: RefineState, settings: MultiViewSettings, gt: torch.Tensor, total_views: int,
+                     group=None, lambda_l1: float = 0.8, loss_impl: str = "fused", do_step: bool = True) -> IterationResult:
+    """One Adam step on `total_views` views, of which this rank renders `settings.viewmatrices.shape[0]`.
+
+    loss = (1/total_views) * sum_v [lambda*L1_v + (1-lambda)*(1-SSIM_v)]; gradients are summed over ranks.
+    """
+    names = [n for n, _ in GROUPS]
+    leaves = []
+    for n in names:
+        p = state.param(n).detach().requires_grad_(True)
+        leaves.append(p)
+    lv = dict(zip(names, leaves))
+    Vl = int(settings.viewmatrices.shape[0]) if settings is not None else 0
+    if Vl > 0:
+        scales = torch.exp(lv["scaling"])
+        rot = F.normalize(lv["rotation"])
+        opac = torch.sigmoid(lv["opacity"])
+        outs = rasterize_views(lv["xyz"], lv["shs"], opac, scales, rot, settings)
+        color, radii = outs[0], outs[1]
+        loss = refine_loss_sum(color, gt, lambda_l1, loss_impl) / float(total_views)
+        grads = torch.autograd.grad(loss, leaves, allow_unused=True)
+        for n, g in zip(names, grads):
+            a, b, _k = state.slices[n]
+            if g is None:
+                state.grad[a:b].zero_()
+            else:
+                state.grad[a:b].copy_(g.reshape(-1))
+        loss = loss.detach()
+        fn = color.grad_fn
+        g2d = getattr(fn, "grad_means2D", None)
+        R = int(getattr(fn, "num_rendered", 0))
+    else:  # a rank without views still takes part in the all-reduce and the Adam step
+        state.grad.zero_()
+        loss = torch.zeros((), device=state.device)
+        radii, g2d, R = torch.zeros(0, state.P, dtype=torch.int32, device=state.device), None, 0
+    if group is not None and torch.distributed.get_world_size(group) > 1:
+        torch.distributed.all_reduce(state.grad, group=group)
+        loss = loss.clone()
+        torch.distributed.all_reduce(loss, group=group)
+    if do_step:
+        state.adam_step()
+    return IterationResult(loss, R, radii, g2d)
+
+
+def shard_views(total_views: int, rank: int, world: int):
+    """View v -> rank v mod world: 20 views on 8 ranks = 3,3,3,3,2,2,2,2."""
+    return list(range(rank, total_views, world))

@@ -197,6 +197,18 @@ int igs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
 
 const char* igs_last_error(void);
 int igs_abi_version(void);
+/* Cumulative number of CUDA kernels this library has launched in this process (bench.py's
+ * `gpu_launches` evidence; the reference has no equivalent). */
+unsigned long long igs_kernel_launches(void);
+
+/* Per-stage device timing for bench.py's roofline (no reference equivalent).  When enabled, every
+ * stage is bracketed by a CUDA event pair on the launching stream; igs_stage_timing_read() resolves
+ * them (it synchronises on the recorded events), fills ms[i] / counts[i] for stage i < n with the
+ * accumulated milliseconds and number of launches, optionally resets the accumulators, and returns
+ * the number of stages.  igs_stage_name(i) names stage i ("blend_fwd", "tile_sort", ...). */
+void igs_stage_timing_enable(int on);
+int igs_stage_timing_read(double* ms, unsigned long long* counts, int n, int reset);
+const char* igs_stage_name(int i);
 
 #ifdef __cplusplus
 }
