@@ -120,6 +120,23 @@ extern "C" {
 
 const char* igs_last_error(void) { return igs::g_err; }
 int igs_abi_version(void) { return IGS_RASTER_ABI_VERSION; }
+int igs_refine_loss(const float* pred, const float* gt, int V, int height, int width, float lambda_l1, float* loss_sum,
+                    float* dL_dpred, igs_alloc_fn temp_alloc, void* temp_user, void* stream) {
+  if (V < 0 || height <= 0 || width <= 0 || !temp_alloc) { set_error("bad argument"); return IGS_ERR_INVALID; }
+  if (V == 0) return IGS_OK;
+  if (!pred || !gt || !loss_sum || !dL_dpred) { set_error("null pointer"); return IGS_ERR_INVALID; }
+  size_t bytes = refine_loss_scratch_bytes(V, height, width);
+  char* tmp = temp_alloc(temp_user, bytes + 256);
+  if (!tmp) { set_error("temp allocator returned NULL"); return IGS_ERR_ALLOC; }
+  tmp = (char*)(((uintptr_t)tmp + 255) & ~uintptr_t(255));
+  {
+    StageScope st(IGS_STAGE_LOSS, (cudaStream_t)stream);
+    launch_refine_loss(pred, gt, V, height, width, lambda_l1, loss_sum, dL_dpred, tmp, (cudaStream_t)stream);
+  }
+  IGS_CUDA_CHECK(cudaGetLastError());
+  return IGS_OK;
+}
+
 void igs_stage_timing_enable(int on) {
   std::lock_guard<std::mutex> lk(igs::g_timer.mu);
   igs::g_timer.on = on != 0;

@@ -123,5 +123,8 @@ void launch_blend_fwd(const BlendFwdParams& p, int V, bool coord, bool depth, cu
 void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s);
 void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s);
 void launch_finish_bwd(const FinishBwdParams& p, cudaStream_t s);
+size_t refine_loss_scratch_bytes(int V, int H, int W);
+void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float* loss_sum,
+                        float* dpred, char* scratch, cudaStream_t s);
 
 }  // namespace igs

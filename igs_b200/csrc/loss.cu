@@ -1,0 +1,211 @@
+// loss.cu — fused refine loss  sum_v [ lambda * L1_v + (1 - lambda) * (1 - SSIM_v) ]  and its gradient w.r.t.
+// the rendered image, replacing the torch ops of the reference refine loop (infer_batch.py:301-305,
+// igs/utils/loss_utils.py:16-62: l1_loss, ssim with an 11x11 Gaussian window sigma 1.5, zero padding,
+// C1 = 0.01^2, C2 = 0.03^2, mean over 3*H*W).
+//
+// Two tiled passes per (view, channel) plane, both separable (11 horizontal + 11 vertical taps through shared
+// memory) instead of the reference's five dense 121-tap grouped convolutions forward and five more backward:
+//   pass 1: mu1, mu2, E[x^2], E[y^2], E[xy] -> SSIM value, |x-y|, and the three per-pixel partials
+//           dS/dmu1, dS/dE11, dS/dE12 (12 B/pixel of scratch);
+//   pass 2: dS/dx(p) = (G * dmu1)(p) + 2 x(p) (G * dE11)(p) + y(p) (G * dE12)(p)   (the window is symmetric and the
+//           padding is zero, so the adjoint of the convolution is the same convolution), combined with the L1 sign.
+// The scalar loss is reduced deterministically: per-block partial sums in double, then one final block.
+#include "common.cuh"
+#include "kernels.cuh"
+
+namespace igs {
+
+#define LOSS_BX 32
+#define LOSS_BY 16
+#define LOSS_R 5
+#define LOSS_TW (LOSS_BX + 2 * LOSS_R)  // 42
+#define LOSS_TH (LOSS_BY + 2 * LOSS_R)  // 26
+
+struct LossParams {
+  int planes, H, W;        // planes = V*3
+  int plane_per_view;      // 3
+  float win[11];           // gauss(x) = exp(-(x-5)^2 / (2*1.5^2)) / sum, computed like loss_utils.py:23-25
+  float lambda;
+  float inv_n;             // 1 / (3*H*W)
+  const float* pred;
+  const float* gt;
+  float* dmu1;             // scratch [planes][H][W]
+  float* dE11;
+  float* dE12;
+  float* dpred;
+  double* partial;         // [gridDim.x*gridDim.y*gridDim.z]
+};
+
+__device__ __forceinline__ float ld_pad(const float* __restrict__ p, int x, int y, int W, int H) {
+  return (x >= 0 && x < W && y >= 0 && y < H) ? p[(size_t)y * W + x] : 0.0f;
+}
+
+__global__ void __launch_bounds__(256)
+loss_pass1_kernel(LossParams p) {
+  __shared__ float sx[LOSS_TH][LOSS_TW + 1];
+  __shared__ float sy[LOSS_TH][LOSS_TW + 1];
+  __shared__ float hb[5][LOSS_TH][LOSS_BX + 1];
+  __shared__ double red[8];
+  const int plane = blockIdx.z;
+  const float* __restrict__ X = p.pred + (size_t)plane * p.H * p.W;
+  const float* __restrict__ Y = p.gt + (size_t)plane * p.H * p.W;
+  const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < LOSS_TH * LOSS_TW; i += 256) {
+    int ty = i / LOSS_TW, tx = i - ty * LOSS_TW;
+    sx[ty][tx] = ld_pad(X, x0 + tx - LOSS_R, y0 + ty - LOSS_R, p.W, p.H);
+    sy[ty][tx] = ld_pad(Y, x0 + tx - LOSS_R, y0 + ty - LOSS_R, p.W, p.H);
+  }
+  __syncthreads();
+  // horizontal
+  for (int i = tid; i < LOSS_TH * LOSS_BX; i += 256) {
+    int ty = i / LOSS_BX, tx = i - ty * LOSS_BX;
+    float a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
+#pragma unroll
+    for (int k = 0; k < 11; k++) {
+      float w = p.win[k], xv = sx[ty][tx + k], yv = sy[ty][tx + k];
+      a0 = fmaf(w, xv, a0); a1 = fmaf(w, yv, a1);
+      a2 = fmaf(w, xv * xv, a2); a3 = fmaf(w, yv * yv, a3); a4 = fmaf(w, xv * yv, a4);
+    }
+    hb[0][ty][tx] = a0; hb[1][ty][tx] = a1; hb[2][ty][tx] = a2; hb[3][ty][tx] = a3; hb[4][ty][tx] = a4;
+  }
+  __syncthreads();
+  // vertical + SSIM + partials
+  double acc = 0.0;
+  const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
+  for (int i = tid; i < LOSS_BY * LOSS_BX; i += 256) {
+    int ty = i / LOSS_BX, tx = i - ty * LOSS_BX;
+    int gx = x0 + tx, gy = y0 + ty;
+    if (gx >= p.W || gy >= p.H) continue;
+    float mu1 = 0, mu2 = 0, e11 = 0, e22 = 0, e12 = 0;
+#pragma unroll
+    for (int k = 0; k < 11; k++) {
+      float w = p.win[k];
+      mu1 = fmaf(w, hb[0][ty + k][tx], mu1); mu2 = fmaf(w, hb[1][ty + k][tx], mu2);
+      e11 = fmaf(w, hb[2][ty + k][tx], e11); e22 = fmaf(w, hb[3][ty + k][tx], e22);
+      e12 = fmaf(w, hb[4][ty + k][tx], e12);
+    }
+    float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+    float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
+    float A = 2.0f * mu12 + C1, B = 2.0f * s12 + C2, Cc = mu1_sq + mu2_sq + C1, D = s1 + s2 + C2;
+    float inv = 1.0f / (Cc * D);
+    float ssim = A * B * inv;
+    // partials of ssim w.r.t. mu1 (E's held fixed), E11, E12
+    float dmu1 = (2.0f * mu2 * B - 2.0f * mu2 * A) * inv - ssim * (2.0f * mu1 * D - 2.0f * mu1 * Cc) * inv;
+    float d11 = -ssim / D;
+    float d12 = 2.0f * A * inv;
+    size_t o = (size_t)plane * p.H * p.W + (size_t)gy * p.W + gx;
+    p.dmu1[o] = dmu1; p.dE11[o] = d11; p.dE12[o] = d12;
+    float xv = sx[ty + LOSS_R][tx + LOSS_R], yv = sy[ty + LOSS_R][tx + LOSS_R];
+    acc += (double)(p.lambda * fabsf(xv - yv)) - (double)((1.0f - p.lambda) * ssim);
+  }
+  // block reduce (fixed order)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((tid & 31) == 0) red[tid >> 5] = acc;
+  __syncthreads();
+  if (tid == 0) {
+    double t = 0;
+    for (int w = 0; w < 8; w++) t += red[w];
+    p.partial[((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = t;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+loss_pass2_kernel(LossParams p) {
+  __shared__ float s0[LOSS_TH][LOSS_TW + 1];
+  __shared__ float s1[LOSS_TH][LOSS_TW + 1];
+  __shared__ float s2[LOSS_TH][LOSS_TW + 1];
+  __shared__ float hb[3][LOSS_TH][LOSS_BX + 1];
+  const int plane = blockIdx.z;
+  const size_t po = (size_t)plane * p.H * p.W;
+  const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
+  const int tid = threadIdx.x;
+  for (int i = tid; i < LOSS_TH * LOSS_TW; i += 256) {
+    int ty = i / LOSS_TW, tx = i - ty * LOSS_TW;
+    int gx = x0 + tx - LOSS_R, gy = y0 + ty - LOSS_R;
+    s0[ty][tx] = ld_pad(p.dmu1 + po, gx, gy, p.W, p.H);
+    s1[ty][tx] = ld_pad(p.dE11 + po, gx, gy, p.W, p.H);
+    s2[ty][tx] = ld_pad(p.dE12 + po, gx, gy, p.W, p.H);
+  }
+  __syncthreads();
+  for (int i = tid; i < LOSS_TH * LOSS_BX; i += 256) {
+    int ty = i / LOSS_BX, tx = i - ty * LOSS_BX;
+    float a0 = 0, a1 = 0, a2 = 0;
+#pragma unroll
+    for (int k = 0; k < 11; k++) {
+      float w = p.win[k];
+      a0 = fmaf(w, s0[ty][tx + k], a0); a1 = fmaf(w, s1[ty][tx + k], a1); a2 = fmaf(w, s2[ty][tx + k], a2);
+    }
+    hb[0][ty][tx] = a0; hb[1][ty][tx] = a1; hb[2][ty][tx] = a2;
+  }
+  __syncthreads();
+  for (int i = tid; i < LOSS_BY * LOSS_BX; i += 256) {
+    int ty = i / LOSS_BX, tx = i - ty * LOSS_BX;
+    int gx = x0 + tx, gy = y0 + ty;
+    if (gx >= p.W || gy >= p.H) continue;
+    float c0 = 0, c1 = 0, c2 = 0;
+#pragma unroll
+    for (int k = 0; k < 11; k++) {
+      float w = p.win[k];
+      c0 = fmaf(w, hb[0][ty + k][tx], c0); c1 = fmaf(w, hb[1][ty + k][tx], c1); c2 = fmaf(w, hb[2][ty + k][tx], c2);
+    }
+    size_t o = po + (size_t)gy * p.W + gx;
+    float xv = p.pred[o], yv = p.gt[o];
+    float dssim = c0 + 2.0f * xv * c1 + yv * c2;
+    float d = xv - yv;
+    float sgn = (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f);   // torch: sign(0) = 0
+    p.dpred[o] = (p.lambda * sgn - (1.0f - p.lambda) * dssim) * p.inv_n;
+  }
+}
+
+__global__ void __launch_bounds__(256)
+loss_final_kernel(const double* __restrict__ partial, size_t n, double inv_n, double constant, float* __restrict__ out) {
+  __shared__ double red[8];
+  double acc = 0.0;
+  for (size_t i = threadIdx.x; i < n; i += 256) acc += partial[i];
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0;
+    for (int w = 0; w < 8; w++) t += red[w];
+    *out = (float)(t * inv_n + constant);
+  }
+}
+
+size_t refine_loss_scratch_bytes(int V, int H, int W) {
+  size_t planes = (size_t)V * 3, N = (size_t)H * W;
+  size_t nblk = planes * ((W + LOSS_BX - 1) / LOSS_BX) * ((H + LOSS_BY - 1) / LOSS_BY);
+  return 3 * planes * N * sizeof(float) + 256 + nblk * sizeof(double) + 256;
+}
+
+void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float* loss_sum,
+                        float* dpred, char* scratch, cudaStream_t s) {
+  LossParams p;
+  {
+    float gf[11], fsum = 0;
+    for (int x = 0; x < 11; x++) gf[x] = (float)exp(-(double)((x - 5) * (x - 5)) / (2.0 * 1.5 * 1.5));
+    for (int x = 0; x < 11; x++) fsum += gf[x];  // torch: float32 tensor divided by its float32 sum
+    for (int x = 0; x < 11; x++) p.win[x] = gf[x] / fsum;
+  }
+  p.planes = V * 3; p.H = H; p.W = W; p.plane_per_view = 3; p.lambda = lambda;
+  p.inv_n = 1.0f / (3.0f * (float)H * (float)W);
+  p.pred = pred; p.gt = gt; p.dpred = dpred;
+  size_t N = (size_t)H * W, planes = (size_t)V * 3;
+  p.dmu1 = reinterpret_cast<float*>(scratch);
+  p.dE11 = p.dmu1 + planes * N;
+  p.dE12 = p.dE11 + planes * N;
+  size_t off = (3 * planes * N * sizeof(float) + 255) & ~size_t(255);
+  p.partial = reinterpret_cast<double*>(scratch + off);
+  dim3 grid((W + LOSS_BX - 1) / LOSS_BX, (H + LOSS_BY - 1) / LOSS_BY, V * 3);
+  count_launch(3);
+  loss_pass1_kernel<<<grid, 256, 0, s>>>(p);
+  loss_pass2_kernel<<<grid, 256, 0, s>>>(p);
+  size_t nblk = (size_t)grid.x * grid.y * grid.z;
+  loss_final_kernel<<<1, 256, 0, s>>>(p.partial, nblk, 1.0 / (3.0 * (double)H * (double)W), (double)V * (1.0 - (double)lambda),
+                                      loss_sum);
+}
+
+}  // namespace igs

@@ -310,7 +310,24 @@ void AdamStep(torch::Tensor& param, const torch::Tensor& grad, torch::Tensor& ex
         "adam_step");
 }
 
+std::tuple<torch::Tensor, torch::Tensor> RefineLoss(const torch::Tensor& pred, const torch::Tensor& gt, double lambda_l1) {
+  TORCH_CHECK(pred.is_cuda() && gt.is_cuda(), "refine_loss needs CUDA tensors (there is no CPU path)");
+  TORCH_CHECK(pred.dim() == 4 && pred.size(1) == 3 && pred.sizes() == gt.sizes(), "pred/gt must be [V,3,H,W]");
+  TORCH_CHECK(pred.scalar_type() == torch::kFloat32 && gt.scalar_type() == torch::kFloat32, "float32 only");
+  const c10::cuda::CUDAGuard guard(pred.device());
+  torch::Tensor p = pred.contiguous(), g = gt.contiguous();
+  torch::Tensor loss = torch::zeros({}, p.options());
+  torch::Tensor dpred = torch::empty_like(p);
+  torch::Tensor temp = torch::empty({0}, torch::TensorOptions().dtype(torch::kByte).device(p.device()));
+  check(igs_refine_loss(p.data_ptr<float>(), g.data_ptr<float>(), (int)p.size(0), (int)p.size(2), (int)p.size(3),
+                        (float)lambda_l1, loss.data_ptr<float>(), dpred.data_ptr<float>(), tensor_alloc, &temp,
+                        (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "refine_loss");
+  return std::make_tuple(loss, dpred);
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
+  m.def("refine_loss", &RefineLoss);
   m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
   m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
   m.def("mark_visible", &markVisible);

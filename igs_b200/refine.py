@@ -188,13 +188,27 @@ def refine_iteration(state: RefineState, settings: MultiViewSettings, gt: torch.
         state.grad.zero_()
         loss = torch.zeros((), device=state.device)
         radii, g2d, R = torch.zeros(0, state.P, dtype=torch.int32, device=state.device), None, 0
-    if group is not None and torch.distributed.get_world_size(group) > 1:
-        torch.distributed.all_reduce(state.grad, group=group)
-        loss = loss.clone()
-        torch.distributed.all_reduce(loss, group=group)
+    loss = reduce_gradients(state.grad, loss, group)
     if do_step:
         state.adam_step()
     return IterationResult(loss, R, radii, g2d)
+
+
+def reduce_gradients(flat_grad: torch.Tensor, loss: torch.Tensor, group=None) -> torch.Tensor:
+    """The one exchange step of the view-sharded iteration: SUM all-reduce of the packed [P*59] gradient
+    buffer (in place) and of the already 1/total_views-scaled partial loss.  Backend-agnostic (NCCL on the GPU
+    box, gloo in the CPU tests)."""
+    if group is None or torch.distributed.get_world_size(group) <= 1:
+        return loss
+    torch.distributed.all_reduce(flat_grad, group=group)
+    loss = loss.clone()
+    torch.distributed.all_reduce(loss, group=group)
+    return loss
+
+
+def pack_gradients(grads: dict, P: int) -> torch.Tensor:
+    """Packs per-parameter gradients into the [P*59] record order of GROUPS."""
+    return torch.cat([grads[n].reshape(P * k) for n, k in GROUPS])
 
 
 def shard_views(total_views: int, rank: int, world: int):

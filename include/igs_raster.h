@@ -195,6 +195,13 @@ int igs_decode_binning(int P, int V, int R, int width, int height,
 int igs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
                   size_t n, float lr, float beta1, float beta2, float eps, int step, void* stream);
 
+/* Fused refine loss over V images [V][3][H][W] (replaces infer_batch.py:301-305 with igs/utils/loss_utils.py:16-62):
+ *   *loss_sum = sum_v [ lambda * mean|pred_v - gt_v| + (1 - lambda) * (1 - mean SSIM(pred_v, gt_v)) ]
+ *   dL_dpred  = d(*loss_sum) / d(pred)            (11x11 Gaussian window, sigma 1.5, zero padding)
+ * loss_sum is a DEVICE float; temp_alloc provides 36*V*H*W bytes (+ a few KB) of scratch. */
+int igs_refine_loss(const float* pred, const float* gt, int V, int height, int width, float lambda_l1,
+                    float* loss_sum, float* dL_dpred, igs_alloc_fn temp_alloc, void* temp_user, void* stream);
+
 const char* igs_last_error(void);
 int igs_abi_version(void);
 /* Cumulative number of CUDA kernels this library has launched in this process (bench.py's

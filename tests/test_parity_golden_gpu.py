@@ -1,0 +1,90 @@
+"""GPU: the CUDA path, called through the drop-in package, against golden vectors from the UNMODIFIED reference
+CUDA rasterizer (tests/golden/ref_*.npz).  Bit-exact: radii, tiles_touched, sorted keys, point_list, ranges,
+n_contrib, depths/means2D/conic.  Maps <= 1e-4 max-abs.  Gradients <= 1e-3 relative (tolerances.py)."""
+import numpy as np
+import pytest
+
+import cases
+from gpu_util import run_case
+from tolerances import GRAD_RTOL, MAP_ATOL, grad_err, well_conditioned_rotation_mask
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module", params=list(cases.CASES))
+def trio(request, cuda_dev, native):
+    import diff_gaussian_rasterization_rade as dgr
+    g = cases.load_golden(request.param)
+    assert g is not None
+    case = cases.case_from_golden(g)
+    return request.param, g, case, run_case(dgr, case, cuda_dev, native=native), dgr
+
+
+def test_bit_exact_binning(trio):
+    _, g, case, out, _ = trio
+    assert out["R"] == int(g["R"])
+    np.testing.assert_array_equal(out["radii"], g["radii"])
+    d = out["decoded"]
+    np.testing.assert_array_equal(d["tiles_touched"].reshape(-1).astype(np.int64), g["tiles_touched"].astype(np.int64))
+    np.testing.assert_array_equal(d["keys"], g["point_list_keys"])
+    np.testing.assert_array_equal(d["point_list"].astype(np.int64), g["point_list"].astype(np.int64))
+    np.testing.assert_array_equal(d["ranges"].astype(np.int64), g["ranges"].astype(np.int64))
+    np.testing.assert_array_equal(d["n_contrib"].reshape(2, -1).astype(np.uint32), g["n_contrib"].astype(np.uint32))
+
+
+def test_bit_exact_preprocess(trio):
+    _, g, case, out, _ = trio
+    vis = g["radii"] > 0
+    P = case["P"]
+    d = out["decoded"]
+    for k, w in (("depths", 1), ("means2D", 2), ("conic_opacity", 4)):
+        a = d[k].reshape(P, w)[vis].view(np.uint32)
+        b = g["geom_" + k].reshape(P, w)[vis].view(np.uint32)
+        assert (a != b).sum() == 0, k
+    for k, w in (("rgb", 3), ("view_points", 3), ("camera_planes", 6), ("ray_planes", 2), ("ts", 1), ("normals", 3)):
+        a = d[k].reshape(P, w)[vis]
+        b = g["geom_" + k].reshape(P, w)[vis]
+        if "colors_precomp" in case and k == "rgb":
+            continue
+        assert np.abs(a - b).max(initial=0) <= 1e-4 * max(1.0, np.abs(b).max(initial=0)), k
+
+
+def test_maps(trio):
+    _, g, case, out, _ = trio
+    for n, m in zip(cases.MAP_NAMES, out["maps"]):
+        assert not np.isnan(m).any()
+        assert np.abs(m - g["map_" + n]).max() <= MAP_ATOL, n
+    # colour and alpha depend only on the bit-pinned chain: they are bit-exact
+    np.testing.assert_array_equal(out["maps"][0], g["map_color"])
+    np.testing.assert_array_equal(out["maps"][5], g["map_alpha"])
+
+
+@pytest.mark.parametrize("which", ["color", "all"])
+def test_gradients(trio, cuda_dev, which):
+    name, g, case, _, dgr = trio
+    out = run_case(dgr, case, cuda_dev, cot=cases.cotangents(case), which=which)
+    for k in cases.GRAD_NAMES:
+        key = f"grad_{which}_{k}"
+        if key not in g:
+            continue
+        ref, got = g[key], out["grads"][k].reshape(g[key].shape)
+        assert not np.isnan(got).any(), k
+        if k == "rotations":
+            m = well_conditioned_rotation_mask(case.get("scales"), scale_modifier=case["scale_modifier"])
+            ref, got = ref[m], got[m]
+        assert grad_err(got, ref) <= GRAD_RTOL, (name, k, grad_err(got, ref))
+
+
+def test_clamp_package_clamps_five_gradients(trio, cuda_dev):
+    # DGRC/diff_gaussian_rasterization_rade_clamp/__init__.py:157-161
+    name, g, case, _, dgr = trio
+    if name != "dense":
+        pytest.skip("one case is enough")
+    import diff_gaussian_rasterization_rade_clamp as dgrc
+    cot = [c * 50.0 for c in cases.cotangents(case)]
+    a = run_case(dgr, case, cuda_dev, cot=cot, which="all")["grads"]
+    b = run_case(dgrc, case, cuda_dev, cot=cot, which="all")["grads"]
+    assert np.abs(a["means3D"]).max() > 15
+    for k in ("means3D", "sh", "opacities", "scales", "rotations"):
+        np.testing.assert_allclose(b[k], np.clip(a[k], -15, 15), rtol=2e-3, atol=1e-3)
+    np.testing.assert_allclose(b["means2D"], a["means2D"], rtol=2e-3, atol=1e-2)

@@ -1,0 +1,108 @@
+"""GPU: the pieces of the refine iteration around the rasterizer — fused L1+SSIM loss kernel vs the reference's
+loss_utils golden and vs torch at image size, fused Adam vs torch.optim.Adam(eps=1e-15), and the iteration itself
+(loss decreases; sharded-by-view gradient sum equals the single batch)."""
+import numpy as np
+import pytest
+import torch
+
+import cases
+
+pytestmark = pytest.mark.gpu
+
+
+def test_fused_loss_matches_reference_golden(cuda_dev, native):
+    g = dict(np.load(cases.GOLDEN_DIR / "refmath_loss.npz"))
+    for name in ("a", "b"):
+        pred = torch.from_numpy(g[f"{name}_pred"]).unsqueeze(0).to(cuda_dev)
+        gt = torch.from_numpy(g[f"{name}_gt"]).unsqueeze(0).to(cuda_dev)
+        loss, dpred = native.refine_loss(pred, gt, 0.8)
+        assert abs(float(loss) - float(g[f"{name}_loss"])) <= 2e-6
+        ref = g[f"{name}_dpred"]
+        assert np.abs(dpred[0].cpu().numpy() - ref).max() <= 1e-3 * np.abs(ref).max()
+
+
+def test_fused_loss_matches_torch_at_image_size(cuda_dev, native):
+    from igs_b200 import refine
+    gen = torch.Generator().manual_seed(5)
+    V, H, W = 2, 1014, 1352
+    pred = torch.rand(V, 3, H, W, generator=gen).to(cuda_dev).requires_grad_(True)
+    gt = torch.rand(V, 3, H, W, generator=gen).to(cuda_dev)
+    ref = refine.refine_loss_torch(pred, gt, 0.8).sum()
+    ref.backward()
+    loss, dpred = native.refine_loss(pred.detach(), gt, 0.8)
+    assert abs(float(loss) - float(ref)) <= 1e-5 * abs(float(ref))
+    assert float((dpred - pred.grad).abs().max()) <= 1e-3 * float(pred.grad.abs().max())
+    # through the autograd wrapper, scaled
+    p2 = pred.detach().clone().requires_grad_(True)
+    (refine.refine_loss_sum(p2, gt, 0.8, "fused") / 7.0).backward()
+    assert float((p2.grad - pred.grad / 7.0).abs().max()) <= 1e-3 * float(pred.grad.abs().max()) / 7.0
+
+
+def test_fused_adam_matches_torch_adam(cuda_dev, native):
+    gen = torch.Generator().manual_seed(9)
+    n = 100_003
+    p0 = torch.randn(n, generator=gen).to(cuda_dev)
+    a = p0.clone()
+    m = torch.zeros_like(a)
+    v = torch.zeros_like(a)
+    b = p0.clone().requires_grad_(True)
+    opt = torch.optim.Adam([b], lr=0.0016, eps=1e-15)
+    for step in range(1, 6):
+        gr = torch.randn(n, generator=gen).to(cuda_dev) * (10.0 ** (step - 3))
+        native.adam_step(a, gr, m, v, 0.0016, 0.9, 0.999, 1e-15, step)
+        b.grad = gr.clone()
+        opt.step()
+        assert float((a - b.detach()).abs().max()) <= 1e-6
+
+
+def _state_and_settings(dev, P, V, W, H, views=None):
+    from igs_b200 import refine, scenes
+    from igs_b200.multiview import MultiViewSettings
+    sc = scenes.make_gaussians(P, 0, -1.8)
+    cams = scenes.make_cameras(V, W, H, 1)
+    views = list(range(V)) if views is None else views
+    st = MultiViewSettings(H, W, cams.tanfovx, cams.tanfovy, 0.0, torch.zeros(3, device=dev), 1.0,
+                           cams.viewmatrix[views].to(dev).contiguous(), cams.projmatrix[views].to(dev).contiguous(), 3,
+                           cams.campos[views].to(dev).contiguous())
+    state = refine.RefineState(sc.xyz, sc.log_scale, sc.rot, sc.opacity_logit, sc.sh, dev)
+    return state, st
+
+
+@pytest.mark.parametrize("loss_impl", ["torch", "fused"])
+def test_refine_iterations_reduce_the_loss(cuda_dev, native, loss_impl):
+    from igs_b200 import refine
+    P, V, W, H = 20000, 4, 160, 120
+    state, st = _state_and_settings(cuda_dev, P, V, W, H)
+    with torch.no_grad():
+        target = refine.forward_views(state, st)[0].clone()
+    # perturb the colours and positions, then refine back towards the target renders
+    gen = torch.Generator().manual_seed(3)
+    state.param("shs").add_(0.3 * torch.randn(P, 16, 3, generator=gen).to(cuda_dev))
+    losses = []
+    for _ in range(25):
+        r = refine.refine_iteration(state, st, target, V, loss_impl=loss_impl)
+        losses.append(float(r.loss))
+    assert losses[-1] < 0.7 * losses[0], losses
+    assert r.radii.shape == (V, P) and r.num_rendered > 0
+
+
+def test_sharded_gradients_equal_single_batch(cuda_dev, native):
+    """What N ranks + all-reduce compute (each rank its views, loss scaled by 1/total_views) summed == one rank
+    rendering all views.  The collective itself is covered by tests/test_dist_gloo.py."""
+    from igs_b200 import refine
+    P, V, W, H = 20000, 5, 160, 120
+    state, st_all = _state_and_settings(cuda_dev, P, V, W, H)
+    gen = torch.Generator().manual_seed(4)
+    gt = torch.rand(V, 3, H, W, generator=gen).to(cuda_dev)
+    r_all = refine.refine_iteration(state, st_all, gt, V, do_step=False)
+    g_all = state.grad.clone()
+    total = torch.zeros_like(g_all)
+    loss = 0.0
+    for rank in range(2):
+        views = refine.shard_views(V, rank, 2)
+        s2, st = _state_and_settings(cuda_dev, P, V, W, H, views)
+        r = refine.refine_iteration(s2, st, gt[views], V, do_step=False)
+        total += s2.grad
+        loss += float(r.loss)
+    assert abs(loss - float(r_all.loss)) <= 1e-5 * abs(loss)
+    assert float((total - g_all).abs().max()) <= 1e-4 * float(g_all.abs().max())
