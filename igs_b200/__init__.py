@@ -22,6 +22,8 @@ __all__ = sorted(_API)
 def __getattr__(name):
     if name in _API:
         return getattr(importlib.import_module("." + _API[name], __name__), name)
+    if name == "_C":
+        import torch  # noqa: F401  libtorch must be loaded by torch itself before the extension that links it
     if name in ("_C", "rasterizer", "multiview", "refine", "scenes", "build"):
         return importlib.import_module("." + name, __name__)
     raise AttributeError(f"module {__name__!r} has no attribute {name!r}")
