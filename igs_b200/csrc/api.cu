@@ -84,6 +84,7 @@ __global__ void write_header_kernel(Header* h, Header v, const uint32_t* total) 
   v.R = total ? *total : 0u;
   *h = v;
 }
+__global__ void write_tag_kernel(BufTag* t, BufTag v) { *t = v; }
 
 __global__ void adam_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m,
                             float* __restrict__ v, size_t n, float b1, float b2, float eps, float step_size,
@@ -187,6 +188,8 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   char* iptr = img_alloc(img_user, isz.bytes);
   if (!iptr) { set_error("image allocator returned NULL for %zu bytes", isz.bytes); return IGS_ERR_ALLOC; }
   ImgBuf I = carve_img(iptr, V, N, tiles);
+  count_launch();
+  write_tag_kernel<<<1, 1, 0, s>>>(I.tag, BufTag{IGS_TAG_IMG, 0u, (uint32_t)V, (uint32_t)N});
 
   count_launch();
   pack_cameras_kernel<<<V, 64, 0, s>>>(V, a->viewmatrix, a->projmatrix, a->cam_pos, G.cams);
@@ -231,6 +234,8 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   char* bptr = bin_alloc(bin_user, bsz.bytes);
   if (!bptr) { set_error("binning allocator returned NULL for %zu bytes", bsz.bytes); return IGS_ERR_ALLOC; }
   BinBuf B = carve_bin(bptr, R);
+  count_launch();
+  write_tag_kernel<<<1, 1, 0, s>>>(B.tag, BufTag{IGS_TAG_BIN, 0u, R, (uint32_t)V});
 
   IGS_CUDA_CHECK(cudaMemsetAsync(I.ranges, 0, sizeof(uint2) * V * tiles, s));
   int bcur = 0;
@@ -285,8 +290,16 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   BinBuf B = carve_bin(a->binning_buffer, R);
   ImgBuf I = carve_img(a->image_buffer, V, N, tiles);
   Header hv;
+  BufTag tb, ti;
   IGS_CUDA_CHECK(cudaMemcpyAsync(&hv, G.hdr, sizeof(Header), cudaMemcpyDeviceToHost, s));
+  IGS_CUDA_CHECK(cudaMemcpyAsync(&tb, B.tag, sizeof(BufTag), cudaMemcpyDeviceToHost, s));
+  IGS_CUDA_CHECK(cudaMemcpyAsync(&ti, I.tag, sizeof(BufTag), cudaMemcpyDeviceToHost, s));
   IGS_CUDA_CHECK(cudaStreamSynchronize(s));
+  if (tb.magic != IGS_TAG_BIN || tb.a != R || ti.magic != IGS_TAG_IMG || ti.a != (uint32_t)V || ti.b != (uint32_t)N) {
+    set_error("binning / image buffer does not belong to this call (tags %x/%u %x/%u/%u, expected R %u V %d N %zu)",
+              tb.magic, tb.a, ti.magic, ti.a, ti.b, R, V, N);
+    return IGS_ERR_INVALID;
+  }
   if (hv.magic != IGS_MAGIC || hv.P != (uint32_t)P || hv.V != (uint32_t)V || hv.N != (uint32_t)N || hv.R != R) {
     set_error("geometry buffer does not match this call (magic %x P %u V %u N %u R %u vs P %d V %d N %zu R %u)",
               hv.magic, hv.P, hv.V, hv.N, hv.R, P, V, N, R);

@@ -131,7 +131,14 @@ __host__ __device__ inline GeomBuf carve_geom(char* base, size_t P, size_t V) {
   return g;
 }
 
+// 16-byte tag at the start of the binning / image buffers so that backward can reject a buffer that does not
+// belong to this call (wrong order, wrong size) instead of reading through it.
+struct BufTag { uint32_t magic, kind, a, b; };
+#define IGS_TAG_BIN 0x42494E31u  // "BIN1"
+#define IGS_TAG_IMG 0x494D4731u  // "IMG1"
+
 struct BinBuf {
+  BufTag* tag;
   uint32_t* tkey[2];   // [R] global tile id (v*tiles + tile), ping-pong
   uint32_t* tval[2];   // [R] emission slot e, ping-pong
   uint32_t* inst_gid;  // [R] emission slot -> global Gaussian id
@@ -145,6 +152,7 @@ __host__ __device__ inline BinBuf carve_bin(char* base, size_t R) {
   BinBuf b;
   Carver c(base);
   size_t Rc = R ? R : 1;
+  b.tag = c.take<BufTag>(1);
   b.tkey[0] = c.take<uint32_t>(Rc);
   b.tkey[1] = c.take<uint32_t>(Rc);
   b.tval[0] = c.take<uint32_t>(Rc);
@@ -158,6 +166,7 @@ __host__ __device__ inline BinBuf carve_bin(char* base, size_t R) {
 }
 
 struct ImgBuf {
+  BufTag* tag;
   uint2* ranges;        // [V*tiles]
   uint32_t* n_contrib;  // [V][2][N]
   float* accum_coord;   // [V][3][N]
@@ -169,6 +178,7 @@ struct ImgBuf {
 __host__ __device__ inline ImgBuf carve_img(char* base, size_t V, size_t N, size_t tiles) {
   ImgBuf m;
   Carver c(base);
+  m.tag = c.take<BufTag>(1);
   m.ranges = c.take<uint2>(V * tiles);
   m.n_contrib = c.take<uint32_t>(V * 2 * N);
   m.accum_coord = c.take<float>(V * 3 * N);

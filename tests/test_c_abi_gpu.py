@@ -50,16 +50,16 @@ def test_forward_backward_through_ctypes(cuda_dev, native):
          ("bg", "means3D", "shs", "opacities", "scales", "rotations", "viewmatrix", "projmatrix", "campos")}
     outs = {n: torch.zeros(c, H, W, device=dev) for n, c in zip(cases.MAP_NAMES, cases.MAP_CH)}
     radii = torch.zeros(P, dtype=torch.int32, device=dev)
-    keep = []
+    keep = {}
 
-    def make_alloc():
+    def make_alloc(name):
         def alloc(user, nbytes):
             t = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=dev)
-            keep.append(t)
+            keep[name] = t
             return (t.data_ptr() + 255) & ~255
         return ALLOC(alloc)
 
-    a_geom, a_bin, a_img, a_tmp = make_alloc(), make_alloc(), make_alloc(), make_alloc()
+    a_geom, a_bin, a_img, a_tmp = make_alloc("geom"), make_alloc("bin"), make_alloc("img"), make_alloc("tmp")
     f = Fwd(P=P, D=3, M=16, V=1, width=W, height=H, background=T["bg"].data_ptr(), means3D=T["means3D"].data_ptr(),
             shs=T["shs"].data_ptr(), colors_precomp=None, opacities=T["opacities"].data_ptr(), scales=T["scales"].data_ptr(),
             scale_modifier=1.0, rotations=T["rotations"].data_ptr(), cov3D_precomp=None, viewmatrix=T["viewmatrix"].data_ptr(),
@@ -77,7 +77,7 @@ def test_forward_backward_through_ctypes(cuda_dev, native):
     np.testing.assert_array_equal(radii.cpu().numpy(), g["radii"])
     for n in cases.MAP_NAMES:
         assert np.abs(outs[n].cpu().numpy() - g["map_" + n]).max() <= MAP_ATOL, n
-    geom, binning, img = keep[0], keep[1], keep[2]
+    geom, binning, img = keep["geom"], keep["bin"], keep["img"]
     al = lambda t: (t.data_ptr() + 255) & ~255  # noqa: E731
     cot = torch.from_numpy(cases.cotangents(case)[0]).to(dev)
     G = dict(m2=torch.empty(P, 3, device=dev), col=torch.empty(P, 3, device=dev), op=torch.empty(P, device=dev),
@@ -100,6 +100,10 @@ def test_forward_backward_through_ctypes(cuda_dev, native):
         ref = g["grad_color_" + k]
         assert grad_err(t.cpu().numpy().reshape(ref.shape), ref) <= GRAD_RTOL, k
     assert lib.igs_kernel_launches() > 0
-    # a mismatching buffer is rejected, not silently used
+    # mismatching buffers are rejected, not read through
     b.R = R.value + 1
-    assert lib.igs_rasterize_backward(C.byref(b), a_tmp, None, C.c_void_p(stream)) != 0
+    assert lib.igs_rasterize_backward(C.byref(b), a_tmp, None, C.c_void_p(stream)) == -1
+    b.R = R.value
+    b.binning_buffer, b.image_buffer = al(img), al(binning)   # swapped
+    assert lib.igs_rasterize_backward(C.byref(b), a_tmp, None, C.c_void_p(stream)) == -1
+    assert b"does not belong" in lib.igs_last_error()

@@ -41,9 +41,13 @@ def test_bit_exact_preprocess(trio):
         a = d[k].reshape(P, w)[vis].view(np.uint32)
         b = g["geom_" + k].reshape(P, w)[vis].view(np.uint32)
         assert (a != b).sum() == 0, k
+    # planes / normals come from the eigen-decomposition of cov3D: undefined (arbitrary in the reference itself) when
+    # two axes coincide or the smallest eigenvalue sits at the 1e-8 branch threshold -> compared where conditioned
+    cond = well_conditioned_rotation_mask(case.get("scales"), scale_modifier=case["scale_modifier"])
     for k, w in (("rgb", 3), ("view_points", 3), ("camera_planes", 6), ("ray_planes", 2), ("ts", 1), ("normals", 3)):
-        a = d[k].reshape(P, w)[vis]
-        b = g["geom_" + k].reshape(P, w)[vis]
+        sel = vis & cond if (k in ("camera_planes", "ray_planes", "normals") and not isinstance(cond, slice)) else vis
+        a = d[k].reshape(P, w)[sel]
+        b = g["geom_" + k].reshape(P, w)[sel]
         if "colors_precomp" in case and k == "rgb":
             continue
         assert np.abs(a - b).max(initial=0) <= 1e-4 * max(1.0, np.abs(b).max(initial=0)), k
