@@ -6,37 +6,22 @@
 //   * instances are culled per tile and per 8x4 warp block with the same conservative alpha-extent
 //     test as the forward kernel, and instances behind every pixel's last contributor are skipped;
 //   * per pair, the (up to 25) per-Gaussian partial derivatives are reduced across the 32 pixels of
-//     a warp with a butterfly reduce-scatter (31 shuffles for 32 slots instead of 5 per value),
-//     accumulated per batch slot in shared memory, and written ONCE per (tile, instance) as a
-//     dense gradient record Grec[e] indexed by the instance's emission slot e.  No global atomics:
-//     the per-Gaussian sum over its tiles is a contiguous read in gather_bwd (preprocess_bwd.cu),
-//     because emission slots of one Gaussian are consecutive.
+//     a warp with a butterfly reduce-scatter (16 / 31 shuffles for all values together instead of 5 per value),
+//     accumulated per batch slot in WARP-PRIVATE shared-memory accumulators (plain load/add/store: float
+//     atomics on shared memory compile to CAS loops), and written ONCE per (tile, instance) as a dense
+//     gradient record Grec[e] indexed by the instance's emission slot e.  No atomics anywhere: the
+//     per-Gaussian sum over its tiles is a contiguous read in gather_bwd (preprocess_bwd.cu), because
+//     emission slots of one Gaussian are consecutive;
+//   * per-warp culling uses the exact minimum of the splat's quadratic form over the warp's 8x4 block
+//     (blend_common.cuh), so instances that cannot reach alpha >= 1/255 on any of its pixels are skipped;
 //   * GEOGRAD=false is the refine-loop case (only the colour map has a cotangent; autograd hands
 //     None for the six geometry maps): 10 instead of 25 values per pair, identical results because
 //     every omitted term is multiplied by an exactly-zero cotangent in the reference.
 #include "common.cuh"
+#include "blend_common.cuh"
 #include "kernels.cuh"
 
 namespace igs {
-
-
-#define BWD_BATCH 128
-
-__device__ __forceinline__ bool alpha_extent_b(float A, float B, float C, float o, float& ex, float& ey) {
-  if (o < 0.00392156862f) return false;
-  float det = A * C - B * B;
-  float tau = __logf(255.0f * o) * 1.0005f + 1e-3f;
-  ex = ey = 3.0e38f;
-  if (det > 0.0f && A > 0.0f && C > 0.0f) {
-    float k = 2.0f * tau / det;
-    float x2 = k * C, y2 = k * A;
-    if (x2 < 1e30f && y2 < 1e30f) {
-      ex = sqrtf(x2) * 1.0005f + 0.01f;
-      ey = sqrtf(y2) * 1.0005f + 0.01f;
-    }
-  }
-  return true;
-}
 
 // Butterfly reduce-scatter of NS per-lane values over the 32 lanes of a warp.
 // NS == 32: afterwards lane L holds sum over lanes of v[L] in v[0].
@@ -67,20 +52,21 @@ __device__ __forceinline__ void warp_reduce_scatter(float (&v)[NS], int lane) {
 template <bool COORD, bool DEPTH, bool NORMAL, bool GEOGRAD>
 __global__ void __launch_bounds__(256)
 blend_bwd_kernel(BlendBwdParams p) {
-  constexpr int NS = GEOGRAD ? 32 : 16;
-  constexpr int NV = GEOGRAD ? 25 : 10;
+  constexpr int NS = GEOGRAD ? 32 : 16;         // floats per gradient record in global memory
+  constexpr int NV = GEOGRAD ? 25 : 10;         // values actually produced per pair
+  constexpr int BATCH = GEOGRAD ? 64 : 128;     // instances staged per round
   constexpr bool GEO = GEOGRAD && (COORD || DEPTH || NORMAL);
-  __shared__ float4 s_ha[BWD_BATCH];
-  __shared__ float4 s_hb[BWD_BATCH];
-  __shared__ float2 s_ext[BWD_BATCH];
-  __shared__ uint32_t s_gid[BWD_BATCH];
-  __shared__ uint32_t s_pos[BWD_BATCH];
-  __shared__ uint32_t s_slot[BWD_BATCH];
-  __shared__ uint32_t s_e[BWD_BATCH];
-  __shared__ float4 s_t[GEO ? BWD_BATCH * 4 : BWD_BATCH];
-  __shared__ float s_grad[BWD_BATCH * NS];
+  // survivors: [0,B) head.a {x, y, conic.x, conic.y}; [B,2B) head.b {conic.z, opacity, r, g};
+  // [2B,3B) {blue, list position (bits), tau, batch slot (bits)}
+  __shared__ float4 s_rec[BATCH * 3];
+  __shared__ float4 s_t[GEO ? BATCH * 4 : 1];
+  __shared__ uint32_t s_gid[BATCH];
+  __shared__ uint32_t s_e[BATCH];
   __shared__ uint32_t s_wcount[8];
   __shared__ uint32_t s_red[8];
+  // per-warp private gradient accumulators [8][BATCH][NV]: no shared-memory atomics (float atomics on shared
+  // memory are CAS loops), summed over the 8 warps when the batch's records are written
+  extern __shared__ float s_acc[];
 
   const int tiles = p.tiles_x * p.tiles_y;
   const int gt = blockIdx.x;
@@ -100,7 +86,11 @@ blend_bwd_kernel(BlendBwdParams p) {
   const float tx1 = (float)(min(txi * IGS_TILE_X + IGS_TILE_X, p.W) - 1);
   const float ty1 = (float)(min(tyi * IGS_TILE_Y + IGS_TILE_Y, p.H) - 1);
   const float bx0 = (float)wx0, by0 = (float)wy0;
-  const float bx1 = (float)(wx0 + 7), by1 = (float)(wy0 + 3);
+  const float bx1 = (float)min(wx0 + 7, p.W - 1), by1 = (float)min(wy0 + 3, p.H - 1);
+  const uint32_t rec_base = smem_addr(s_rec);
+  const uint32_t tail_base = smem_addr(s_t);
+  const uint32_t acc_base = smem_addr(s_acc) + (uint32_t)w * (BATCH * NV * 4);
+  for (uint32_t f = threadIdx.x; f < 8 * BATCH * NV; f += 256) s_acc[f] = 0.0f;
 
   const uint2 range = p.ranges[gt];
   const uint32_t last_contributor = inside ? p.n_contrib[(size_t)v * 2 * N + pix_id] : 0u;
@@ -189,13 +179,12 @@ blend_bwd_kernel(BlendBwdParams p) {
   float nr0 = 0, nr1 = 0, nr2 = 0, ln0 = 0, ln1 = 0, ln2 = 0;      // normal recurrence
 
   for (uint32_t hi = end; hi > range.x;) {
-    const uint32_t lo = (hi - range.x > BWD_BATCH) ? hi - BWD_BATCH : range.x;
+    const uint32_t lo = (hi - range.x > BATCH) ? hi - BATCH : range.x;
     const uint32_t nb = hi - lo;
     // ---- 1. fetch (back to front), tile cull, ordered compaction ----
-    for (uint32_t f = threadIdx.x; f < BWD_BATCH * NS; f += 256) s_grad[f] = 0.0f;
     bool keep = false;
     float4 ha, hb;
-    float ex = 0, ey = 0;
+    float ex = 0, ey = 0, tau = 0;
     uint32_t gid = 0, j = 0;
     if (threadIdx.x < nb) {
       j = hi - 1 - threadIdx.x;
@@ -203,7 +192,7 @@ blend_bwd_kernel(BlendBwdParams p) {
       s_e[threadIdx.x] = p.point_e[j];
       ha = p.head[gid].a;
       hb = p.head[gid].b;
-      keep = alpha_extent_b(ha.z, ha.w, hb.x, hb.y, ex, ey);
+      keep = alpha_extent(ha.z, ha.w, hb.x, hb.y, ex, ey, tau);
       keep = keep && (ha.x + ex >= tx0) && (ha.x - ex <= tx1) && (ha.y + ey >= ty0) && (ha.y - ey <= ty1);
     }
     uint32_t bal = __ballot_sync(0xffffffffu, keep);
@@ -218,12 +207,10 @@ blend_bwd_kernel(BlendBwdParams p) {
     }
     if (keep) {
       uint32_t k = woff + __popc(bal & ((1u << lane) - 1u));
-      s_ha[k] = ha;
-      s_hb[k] = hb;
-      s_ext[k] = make_float2(ex, ey);
+      s_rec[k] = ha;
+      s_rec[BATCH + k] = hb;
+      s_rec[2 * BATCH + k] = make_float4(p.tail[gid].a.x, __uint_as_float(j - range.x + 1), tau, __uint_as_float(threadIdx.x));
       s_gid[k] = gid;
-      s_pos[k] = j - range.x + 1;
-      s_slot[k] = threadIdx.x;
     }
     __syncthreads();
     if constexpr (GEO) {
@@ -231,28 +218,28 @@ blend_bwd_kernel(BlendBwdParams p) {
         uint32_t k = f >> 2, q = f & 3;
         s_t[f] = reinterpret_cast<const float4*>(p.tail + s_gid[k])[q];
       }
-    } else {
-      if (threadIdx.x < count) s_t[threadIdx.x].x = p.tail[s_gid[threadIdx.x]].a.x;
+      __syncthreads();
     }
-    __syncthreads();
     // ---- 2. per-warp traversal ----
     for (uint32_t base = 0; base < count; base += 32) {
       uint32_t k = base + lane;
       bool hit = false;
       if (k < count) {
-        float4 a = s_ha[k];
-        float2 e = s_ext[k];
-        hit = (s_pos[k] <= wlast) && (a.x + e.x >= bx0) && (a.x - e.x <= bx1) && (a.y + e.y >= by0) &&
-              (a.y - e.y <= by1);
+        const uint32_t ak = rec_base + k * 16;
+        const float4 a = lds128<0>(ak);
+        const float4 b = lds128<BATCH * 16>(ak);
+        const float4 c = lds128<BATCH * 32>(ak);
+        hit = (__float_as_uint(c.y) <= wlast) && block_can_contribute(a.x, a.y, a.z, a.w, b.x, c.z, bx0, by0, bx1, by1);
       }
       uint32_t m = __ballot_sync(0xffffffffu, hit);
       while (m) {
-        int b = __ffs(m) - 1;
+        const uint32_t kk = base + (__ffs(m) - 1);
         m &= m - 1;
-        const uint32_t kk = base + b;
-        const uint32_t pos = s_pos[kk];
-        const float4 a = s_ha[kk];
-        const float4 bq = s_hb[kk];
+        const uint32_t ak = rec_base + kk * 16;
+        const float4 a = lds128<0>(ak);
+        const float4 bq = lds128<BATCH * 16>(ak);
+        const float4 cq = lds128<BATCH * 32>(ak);  // {blue, position, tau, slot}
+        const uint32_t pos = __float_as_uint(cq.y);
         const float dx = fsub(a.x, pixfx), dy = fsub(a.y, pixfy);
         const float power = splat_power(dx, dy, a.z, a.w, bq.x);
         const float G = expf(power);
@@ -264,11 +251,12 @@ blend_bwd_kernel(BlendBwdParams p) {
 #pragma unroll
         for (int i = 0; i < NS; i++) val[i] = 0.0f;
         if (active) {
-          T = T / (1.0f - alpha);
+          // reference: T = T / (1 - alpha) and (-T_final / (1 - alpha)); one reciprocal serves both
+          const float rcp = __fdividef(1.0f, 1.0f - alpha);
+          T = T * rcp;
           const float aT = alpha * T;
           float dL_dopa = 0.0f;
-          float blue;
-          if constexpr (GEO) blue = s_t[kk * 4].x; else blue = s_t[kk].x;
+          const float blue = cq.x;
           // colour
           ar0 = last_alpha * lc0 + (1.0f - last_alpha) * ar0; lc0 = bq.z; dL_dopa += (bq.z - ar0) * dLp0;
           ar1 = last_alpha * lc1 + (1.0f - last_alpha) * ar1; lc1 = bq.w; dL_dopa += (bq.w - ar1) * dLp1;
@@ -276,7 +264,8 @@ blend_bwd_kernel(BlendBwdParams p) {
           val[0] = aT * dLp0; val[1] = aT * dLp1; val[2] = aT * dLp2;
           float dL_ddelx_geo = 0.0f, dL_ddely_geo = 0.0f;
           if constexpr (GEO) {
-            const float4 t0 = s_t[kk * 4 + 0], t1 = s_t[kk * 4 + 1], t2 = s_t[kk * 4 + 2], t3 = s_t[kk * 4 + 3];
+            const uint32_t at = tail_base + kk * 64;
+            const float4 t0 = lds128<0>(at), t1 = lds128<16>(at), t2 = lds128<32>(at), t3 = lds128<48>(at);
             const bool median = (pos == max_contributor);
             if constexpr (COORD) {
               float c0 = t1.w + t2.z * dx + t2.w * dy;
@@ -316,7 +305,7 @@ blend_bwd_kernel(BlendBwdParams p) {
           dL_dopa += (1.0f - accum_alpha_rec) * dL_dalpha;
           dL_dopa *= T;
           last_alpha = alpha;
-          dL_dopa += (-T_final / (1.0f - alpha)) * bg_dot_dpixel;
+          dL_dopa += (-T_final * rcp) * bg_dot_dpixel;
 
           const float dL_dG = bq.y * dL_dopa;
           const float gdx = G * dx, gdy = G * dy;
@@ -332,16 +321,28 @@ blend_bwd_kernel(BlendBwdParams p) {
           val[9] = G * dL_dopa;
         }
         warp_reduce_scatter<NS>(val, lane);
-        const int slot = GEOGRAD ? lane : (lane >> 1);
-        if (slot < NV && (GEOGRAD || (lane & 1) == 0))
-          atomicAdd(&s_grad[s_slot[kk] * NS + slot], val[0]);
+        // lane -> value index: NS == 32: lane; NS == 16: lanes 2s, 2s+1 both hold value s (even lane stores)
+        const int vi = GEOGRAD ? lane : (lane >> 1);
+        if (vi < NV && (GEOGRAD || (lane & 1) == 0)) {
+          const uint32_t aa = acc_base + (__float_as_uint(cq.w) * NV + vi) * 4;
+          sts32<0>(aa, lds32<0>(aa) + val[0]);
+        }
       }
     }
     __syncthreads();
-    // ---- 3. one dense record per instance of this batch ----
-    for (uint32_t f = threadIdx.x; f < nb * (NS / 4); f += 256) {
-      uint32_t sl = f / (NS / 4), q = f % (NS / 4);
-      reinterpret_cast<float4*>(p.grec + (size_t)s_e[sl] * NS)[q] = reinterpret_cast<const float4*>(s_grad + sl * NS)[q];
+    // ---- 3. one dense record per instance of this batch: sum (and clear) the 8 warps' accumulators ----
+    for (uint32_t f = threadIdx.x; f < nb * NS; f += 256) {
+      const uint32_t sl = f / NS, q = f % NS;
+      float sum = 0.0f;
+      if (q < NV) {
+#pragma unroll
+        for (int ww = 0; ww < 8; ww++) {
+          float* pa = s_acc + ((size_t)ww * BATCH + sl) * NV + q;
+          sum += *pa;
+          *pa = 0.0f;
+        }
+      }
+      p.grec[(size_t)s_e[sl] * NS + q] = sum;
     }
     __syncthreads();
     hi = lo;
@@ -350,19 +351,22 @@ blend_bwd_kernel(BlendBwdParams p) {
 
 int blend_bwd_record_floats(bool geograd) { return geograd ? 32 : 16; }
 
+template <bool C, bool D, bool N, bool G>
+static void launch_one(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
+  constexpr int bytes = 8 * (G ? 64 : 128) * (G ? 25 : 10) * 4;  // per-warp accumulators (dynamic shared memory)
+  // > 48 KB of dynamic shared memory needs the opt-in; it is per device, so it is (cheaply) set on every launch
+  cudaFuncSetAttribute(blend_bwd_kernel<C, D, N, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  blend_bwd_kernel<C, D, N, G><<<nblocks, 256, bytes, s>>>(p);
+}
+
 void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s) {
   int nblocks = V * p.tiles_x * p.tiles_y;
   if (nblocks <= 0) return;
   count_launch();
-  if (!geograd || (!coord && !depth)) {
-    blend_bwd_kernel<false, false, false, false><<<nblocks, 256, 0, s>>>(p);
-  } else if (coord && depth) {
-    blend_bwd_kernel<true, true, true, true><<<nblocks, 256, 0, s>>>(p);
-  } else if (coord) {
-    blend_bwd_kernel<true, false, true, true><<<nblocks, 256, 0, s>>>(p);
-  } else {
-    blend_bwd_kernel<false, true, true, true><<<nblocks, 256, 0, s>>>(p);
-  }
+  if (!geograd || (!coord && !depth)) launch_one<false, false, false, false>(p, nblocks, s);
+  else if (coord && depth) launch_one<true, true, true, true>(p, nblocks, s);
+  else if (coord) launch_one<true, false, true, true>(p, nblocks, s);
+  else launch_one<false, true, true, true>(p, nblocks, s);
 }
 
 }  // namespace igs

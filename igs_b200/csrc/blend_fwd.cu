@@ -13,42 +13,22 @@
 // The per-pixel arithmetic that decides alpha / T / termination is pinned to the reference's
 // compiled operation order (common.cuh splat_power; expf, not __expf), so n_contrib is bit-exact.
 #include "common.cuh"
+#include "blend_common.cuh"
 #include "kernels.cuh"
 
 namespace igs {
 
-
 #define BLEND_BATCH 256
-
-// Conservative half-extents of { d : alpha(d) >= 1/255 } for conic (A,B,C) and opacity o.
-// Returns false if the splat can never reach alpha >= 1/255.  Non-PSD / non-finite conics get
-// infinite extents (never culled) so the exact per-pixel test decides.
-__device__ __forceinline__ bool alpha_extent(float A, float B, float C, float o, float& ex, float& ey) {
-  if (o < 0.00392156862f) return false;  // o*G <= o < 1/255 for every G in [0,1]
-  float det = A * C - B * B;
-  float tau = __logf(255.0f * o) * 1.0005f + 1e-3f;
-  ex = ey = 3.0e38f;
-  if (det > 0.0f && A > 0.0f && C > 0.0f) {
-    float k = 2.0f * tau / det;
-    float x2 = k * C, y2 = k * A;
-    if (x2 < 1e30f && y2 < 1e30f) {
-      ex = sqrtf(x2) * 1.0005f + 0.01f;
-      ey = sqrtf(y2) * 1.0005f + 0.01f;
-    }
-  }
-  return true;
-}
 
 template <bool COORD, bool DEPTH, bool NORMAL>
 __global__ void __launch_bounds__(256)
 blend_fwd_kernel(BlendFwdParams p) {
   constexpr bool GEO = COORD || DEPTH || NORMAL;
-  __shared__ float4 s_ha[BLEND_BATCH];   // x, y, conic.x, conic.y
-  __shared__ float4 s_hb[BLEND_BATCH];   // conic.z, opacity, r, g
-  __shared__ float2 s_ext[BLEND_BATCH];
+  // survivors of the current batch: [0,256) head.a {x, y, conic.x, conic.y}; [256,512) head.b {conic.z, opacity, r, g};
+  // [512,768) {blue, list position (bits), tau, -}
+  __shared__ float4 s_rec[BLEND_BATCH * 3];
+  __shared__ float4 s_t[GEO ? BLEND_BATCH * 4 : 1];  // tails of the survivors
   __shared__ uint32_t s_gid[BLEND_BATCH];
-  __shared__ uint32_t s_pos[BLEND_BATCH];
-  __shared__ float4 s_t[GEO ? BLEND_BATCH * 4 : BLEND_BATCH];
   __shared__ uint32_t s_wcount[8];
 
   const int tiles = p.tiles_x * p.tiles_y;
@@ -70,10 +50,12 @@ blend_fwd_kernel(BlendFwdParams p) {
   const float tx1 = (float)(min(txi * IGS_TILE_X + IGS_TILE_X, p.W) - 1);
   const float ty1 = (float)(min(tyi * IGS_TILE_Y + IGS_TILE_Y, p.H) - 1);
   const float bx0 = (float)wx0, by0 = (float)wy0;
-  const float bx1 = (float)(wx0 + 7), by1 = (float)(wy0 + 3);
+  const float bx1 = (float)min(wx0 + 7, p.W - 1), by1 = (float)min(wy0 + 3, p.H - 1);
+  const uint32_t rec_base = smem_addr(s_rec);
+  const uint32_t tail_base = smem_addr(s_t);
 
   const uint2 range = p.ranges[gt];
-  bool done = !inside;
+  int done = inside ? 0 : 1;
 
   float T = 1.0f;
   uint32_t last_contributor = 0, max_contributor = 0xFFFFFFFFu;
@@ -83,18 +65,18 @@ blend_fwd_kernel(BlendFwdParams p) {
   float N0 = 0, N1 = 0, N2 = 0;
 
   for (uint32_t start = range.x; start < range.y; start += BLEND_BATCH) {
-    if (__syncthreads_count(done) == 256) break;
+    if (__syncthreads_count(done != 0) == 256) break;
     // ---- 1. fetch + tile-level cull + ordered compaction ----
     uint32_t j = start + threadIdx.x;
     bool keep = false;
     float4 ha, hb;
-    float ex = 0, ey = 0;
+    float ex = 0, ey = 0, tau = 0;
     uint32_t gid = 0;
     if (j < range.y) {
       gid = p.point_list[j];
       ha = p.head[gid].a;
       hb = p.head[gid].b;
-      keep = alpha_extent(ha.z, ha.w, hb.x, hb.y, ex, ey);
+      keep = alpha_extent(ha.z, ha.w, hb.x, hb.y, ex, ey, tau);
       keep = keep && (ha.x + ex >= tx0) && (ha.x - ex <= tx1) && (ha.y + ey >= ty0) && (ha.y - ey <= ty1);
     }
     uint32_t bal = __ballot_sync(0xffffffffu, keep);
@@ -109,11 +91,11 @@ blend_fwd_kernel(BlendFwdParams p) {
     }
     if (keep) {
       uint32_t k = woff + __popc(bal & ((1u << lane) - 1u));
-      s_ha[k] = ha;
-      s_hb[k] = hb;
-      s_ext[k] = make_float2(ex, ey);
+      s_rec[k] = ha;
+      s_rec[BLEND_BATCH + k] = hb;
+      // blue lives in the tail record; 1-based list position = the reference's `contributor`
+      s_rec[2 * BLEND_BATCH + k] = make_float4(p.tail[gid].a.x, __uint_as_float(j - range.x + 1), tau, 0.0f);
       s_gid[k] = gid;
-      s_pos[k] = j - range.x + 1;  // 1-based position = reference `contributor`
     }
     __syncthreads();
     // ---- 2. tails of the survivors ----
@@ -122,42 +104,42 @@ blend_fwd_kernel(BlendFwdParams p) {
         uint32_t k = f >> 2, q = f & 3;
         s_t[f] = reinterpret_cast<const float4*>(p.tail + s_gid[k])[q];
       }
-    } else {
-      if (threadIdx.x < count) s_t[threadIdx.x].x = p.tail[s_gid[threadIdx.x]].a.x;  // blue
+      __syncthreads();
     }
-    __syncthreads();
     // ---- 3. per-warp cull + blend ----
-    if (!__all_sync(0xffffffffu, done)) {
+    if (!__all_sync(0xffffffffu, done != 0)) {
       for (uint32_t base = 0; base < count; base += 32) {
         uint32_t k = base + lane;
         bool hit = false;
         if (k < count) {
-          float4 a = s_ha[k];
-          float2 e = s_ext[k];
-          hit = (a.x + e.x >= bx0) && (a.x - e.x <= bx1) && (a.y + e.y >= by0) && (a.y - e.y <= by1);
+          const uint32_t ak = rec_base + k * 16;
+          float4 a = lds128<0>(ak);
+          float4 b = lds128<BLEND_BATCH * 16>(ak);
+          float tk = lds32<BLEND_BATCH * 32 + 8>(ak);
+          hit = block_can_contribute(a.x, a.y, a.z, a.w, b.x, tk, bx0, by0, bx1, by1);
         }
         uint32_t m = __ballot_sync(0xffffffffu, hit);
         while (m) {
-          int b = __ffs(m) - 1;
+          const uint32_t kk = base + (__ffs(m) - 1);
           m &= m - 1;
-          uint32_t kk = base + b;
           if (done) continue;
-          float4 a = s_ha[kk];
-          float4 bq = s_hb[kk];
-          float dx = fsub(a.x, pixfx), dy = fsub(a.y, pixfy);
-          float power = splat_power(dx, dy, a.z, a.w, bq.x);
+          const uint32_t ak = rec_base + kk * 16;
+          const float4 a = lds128<0>(ak);
+          const float4 bq = lds128<BLEND_BATCH * 16>(ak);
+          const float dx = fsub(a.x, pixfx), dy = fsub(a.y, pixfy);
+          const float power = splat_power(dx, dy, a.z, a.w, bq.x);
           if (power > 0.0f) continue;
-          float alpha = fminf(0.99f, fmul(bq.y, expf(power)));
+          const float alpha = fminf(0.99f, fmul(bq.y, expf(power)));
           if (alpha < 1.0f / 255.0f) continue;
-          float test_T = fmul(T, fsub(1.0f, alpha));
-          if (test_T < 0.0001f) { done = true; continue; }
-          float aT = fmul(alpha, T);
-          uint32_t contributor = s_pos[kk];
-          float blue;
-          bool before_median = T > 0.5f;
+          const float test_T = fmul(T, fsub(1.0f, alpha));
+          if (test_T < 0.0001f) { done = 1; continue; }
+          const float aT = fmul(alpha, T);
+          const float2 bp = lds64<BLEND_BATCH * 32>(ak);  // {blue, position}
+          const uint32_t contributor = __float_as_uint(bp.y);
+          const bool before_median = T > 0.5f;
           if constexpr (GEO) {
-            float4 t0 = s_t[kk * 4 + 0], t1 = s_t[kk * 4 + 1], t2 = s_t[kk * 4 + 2], t3 = s_t[kk * 4 + 3];
-            blue = t0.x;
+            const uint32_t at = tail_base + kk * 64;
+            const float4 t0 = lds128<0>(at), t1 = lds128<16>(at), t2 = lds128<32>(at), t3 = lds128<48>(at);
             if constexpr (COORD) {
               float c0 = ffma(dy, t2.w, ffma(dx, t2.z, t1.w));
               float c1 = ffma(dy, t3.y, ffma(dx, t3.x, t2.x));
@@ -174,15 +156,13 @@ blend_fwd_kernel(BlendFwdParams p) {
               N0 += t1.x * aT; N1 += t1.y * aT; N2 += t1.z * aT;
             }
             if (before_median) max_contributor = contributor;
-          } else {
-            blue = s_t[kk].x;
           }
-          C0 = ffma(aT, bq.z, C0); C1 = ffma(aT, bq.w, C1); C2 = ffma(aT, blue, C2);
+          C0 = ffma(aT, bq.z, C0); C1 = ffma(aT, bq.w, C1); C2 = ffma(aT, bp.x, C2);
           weight += aT;
           T = test_T;
           last_contributor = contributor;
         }
-        if (__all_sync(0xffffffffu, done)) break;
+        if (__all_sync(0xffffffffu, done != 0)) break;
       }
     }
   }
