@@ -67,6 +67,8 @@ blend_bwd_kernel(BlendBwdParams p) {
   // per-warp private gradient accumulators [8][BATCH][NV]: no shared-memory atomics (float atomics on shared
   // memory are CAS loops), summed over the 8 warps when the batch's records are written
   extern __shared__ float s_acc[];
+  // colour-only path: per-warp [10][36] transpose staging for the cross-pixel reduction (columns 32..35 stay zero)
+  __shared__ __align__(16) float s_stage[GEOGRAD ? 4 : 8 * 10 * 36];
 
   const int tiles = p.tiles_x * p.tiles_y;
   const int gt = blockIdx.x;
@@ -91,6 +93,14 @@ blend_bwd_kernel(BlendBwdParams p) {
   const uint32_t tail_base = smem_addr(s_t);
   const uint32_t acc_base = smem_addr(s_acc) + (uint32_t)w * (BATCH * NV * 4);
   for (uint32_t f = threadIdx.x; f < 8 * BATCH * NV; f += 256) s_acc[f] = 0.0f;
+  if constexpr (!GEOGRAD) {
+    for (uint32_t f = threadIdx.x; f < 8 * 10 * 36; f += 256) s_stage[f] = 0.0f;
+  }
+  const uint32_t stage_base = smem_addr(s_stage) + (GEOGRAD ? 0u : (uint32_t)w * (10 * 36 * 4));
+  // reduction role of this lane in the colour-only path: value rv = lane / 3, segment rs = lane % 3 (12 pixels each)
+  const uint32_t rv = (uint32_t)lane / 3u, rs = (uint32_t)lane - rv * 3u;
+  const uint32_t stage_wr = stage_base + (uint32_t)lane * 4;
+  const uint32_t stage_rd = stage_base + (rv * 36 + rs * 12) * 4;
 
   const uint2 range = p.ranges[gt];
   const uint32_t last_contributor = inside ? p.n_contrib[(size_t)v * 2 * N + pix_id] : 0u;
@@ -247,12 +257,13 @@ blend_bwd_kernel(BlendBwdParams p) {
         const bool active = (pos <= last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
         if (!__any_sync(0xffffffffu, active)) continue;
 
-        float val[NS];
+        float val[GEOGRAD ? NS : NV];
 #pragma unroll
-        for (int i = 0; i < NS; i++) val[i] = 0.0f;
+        for (int i = 0; i < (GEOGRAD ? NS : NV); i++) val[i] = 0.0f;
         if (active) {
           // reference: T = T / (1 - alpha) and (-T_final / (1 - alpha)); one reciprocal serves both
-          const float rcp = __fdividef(1.0f, 1.0f - alpha);
+          float rcp;
+          asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp) : "f"(1.0f - alpha));  // 1 - alpha is in [0.01, 1]
           T = T * rcp;
           const float aT = alpha * T;
           float dL_dopa = 0.0f;
@@ -320,12 +331,31 @@ blend_bwd_kernel(BlendBwdParams p) {
           val[8] = -0.5f * gdy * dy * dL_dG;
           val[9] = G * dL_dopa;
         }
-        warp_reduce_scatter<NS>(val, lane);
-        // lane -> value index: NS == 32: lane; NS == 16: lanes 2s, 2s+1 both hold value s (even lane stores)
-        const int vi = GEOGRAD ? lane : (lane >> 1);
-        if (vi < NV && (GEOGRAD || (lane & 1) == 0)) {
-          const uint32_t aa = acc_base + (__float_as_uint(cq.w) * NV + vi) * 4;
-          sts32<0>(aa, lds32<0>(aa) + val[0]);
+        if constexpr (GEOGRAD) {
+          warp_reduce_scatter<NS>(val, lane);  // afterwards lane L holds the warp sum of value L
+          if (lane < NV) {
+            const uint32_t aa = acc_base + (__float_as_uint(cq.w) * NV + lane) * 4;
+            sts32<0>(aa, lds32<0>(aa) + val[0]);
+          }
+        } else {
+          // transpose through shared memory: 10 conflict-free stores, then lane (rv, rs) sums 12 pixels of value
+          // rv with three 16-byte loads and the three segments are combined with two shuffles
+          sts32<0 * 144>(stage_wr, val[0]); sts32<1 * 144>(stage_wr, val[1]); sts32<2 * 144>(stage_wr, val[2]);
+          sts32<3 * 144>(stage_wr, val[3]); sts32<4 * 144>(stage_wr, val[4]); sts32<5 * 144>(stage_wr, val[5]);
+          sts32<6 * 144>(stage_wr, val[6]); sts32<7 * 144>(stage_wr, val[7]); sts32<8 * 144>(stage_wr, val[8]);
+          sts32<9 * 144>(stage_wr, val[9]);
+          __syncwarp();
+          float sum = 0.0f;
+          if (lane < 30) {
+            const float4 x0 = lds128<0>(stage_rd), x1 = lds128<16>(stage_rd), x2 = lds128<32>(stage_rd);
+            sum = ((x0.x + x0.y) + (x0.z + x0.w)) + ((x1.x + x1.y) + (x1.z + x1.w)) + ((x2.x + x2.y) + (x2.z + x2.w));
+          }
+          sum += __shfl_down_sync(0xffffffffu, sum, 1) + __shfl_down_sync(0xffffffffu, sum, 2);
+          if (rs == 0 && lane < 30) {
+            const uint32_t aa = acc_base + (__float_as_uint(cq.w) * NV + rv) * 4;
+            sts32<0>(aa, lds32<0>(aa) + sum);
+          }
+          __syncwarp();
         }
       }
     }
