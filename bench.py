@@ -53,6 +53,8 @@ def parse():
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-views", type=int, default=1)
+    ap.add_argument("--no-balance", dest="balance", action="store_false",
+                    help="assign view v to rank v mod N instead of balancing by per-view instance counts")
     return ap.parse_args()
 
 
@@ -221,7 +223,14 @@ def main():
     # ---- synthetic, seeded inputs, generated on the host ----
     sc = scenes.make_gaussians(P, 0, cfg["log_scale_mean"])
     cams = scenes.make_cameras(V, W, H, 1)
+    assignment = "v mod N"
     my_views = refine.shard_views(V, rank, world)
+    if world > 1 and args.balance:
+        # cost-balanced assignment: every rank measures the instance count R_v of each view with a forward-only
+        # pass (deterministic, so all ranks derive the same table) and views are packed greedily (LPT)
+        costs = measure_view_costs(cfg, cams, sc, torch.device("cuda", local_rank))
+        my_views = refine.shard_views_balanced(costs, rank, world)
+        assignment = "LPT on per-view instance counts"
     Vl = len(my_views)
     g = torch.Generator().manual_seed(2 + 1000 * rank)
     gt_host = torch.rand(max(Vl, 1), 3, H, W, generator=g).pin_memory()
@@ -251,11 +260,38 @@ def main():
     def step_resident():
         return refine.refine_iteration(state, st, gt_local, V, group=group, loss_impl=loss_impl)
 
+    # End-to-end step: this step's parameters, cameras and target images come from pinned HOST memory and the loss
+    # goes back to the host.  The copies run on a side stream into double-buffered staging, so the H2D of step k+1
+    # overlaps the kernels of step k (every step still copies all of its own inputs inside the timed region).
+    copy_stream = torch.cuda.Stream(device=dev)
+    stage = [dict(params=torch.empty_like(state.flat), cams=torch.empty_like(cam_dev), gt=torch.empty_like(gt_dev),
+                  ready=torch.cuda.Event(), free=torch.cuda.Event()) for _ in range(2)]
+    e2e_state = {"k": 0, "primed": False}
+
+    def prefetch(slot):
+        b = stage[slot]
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(b["free"])          # the step that last used this slot has finished reading it
+            b["params"].copy_(params_host, non_blocking=True)
+            b["cams"].copy_(cam_host, non_blocking=True)
+            b["gt"].copy_(gt_host, non_blocking=True)
+            b["ready"].record(copy_stream)
+
     def step_e2e():
-        state.load_flat(params_host)
-        cam_dev.copy_(cam_host, non_blocking=True)
-        gt_dev.copy_(gt_host, non_blocking=True)
-        r = refine.refine_iteration(state, settings_from(cam_dev), gt_dev[:Vl], V, group=group, loss_impl=loss_impl)
+        k = e2e_state["k"]
+        if not e2e_state["primed"]:
+            for b in stage:
+                b["free"].record(torch.cuda.current_stream())
+            prefetch(k % 2)
+            e2e_state["primed"] = True
+        b = stage[k % 2]
+        prefetch((k + 1) % 2)                          # next step's inputs, overlapped with this step's kernels
+        cur = torch.cuda.current_stream()
+        cur.wait_event(b["ready"])
+        state.flat.copy_(b["params"])
+        r = refine.refine_iteration(state, settings_from(b["cams"]), b["gt"][:Vl], V, group=group, loss_impl=loss_impl)
+        b["free"].record(cur)
+        e2e_state["k"] = k + 1
         return float(r.loss.item())  # D2H read of the step's result
 
     def barrier():
@@ -296,6 +332,15 @@ def main():
     _C.stage_timing_enable(False)
     R_local = last.num_rendered
     loss_val = float(last.loss.item())
+    # per-rank load (views, instances, device ms spent in this library's stages per step)
+    my_ms = sum(ms for _n, ms, c in stages if c > 0) / args.steps
+    per_rank = torch.tensor([float(Vl), float(R_local), my_ms], device=dev, dtype=torch.float64)
+    if world > 1:
+        allr = [torch.zeros_like(per_rank) for _ in range(world)]
+        dist.all_gather(allr, per_rank)
+    else:
+        allr = [per_rank]
+    per_rank = [{"views": int(t[0]), "R": int(t[1]), "stage_ms": round(float(t[2]), 3)} for t in allr]
 
     # ---- (2) forward-only throughput ----
     def fwd_only():
@@ -303,6 +348,13 @@ def main():
             return refine.forward_views(state, st) if Vl else None
     ms_fwd, _ = timed(fwd_only, max(3, args.steps // 2), 2)
     fwd_mpix = V * N / 1e6 / (ms_fwd / 1e3)
+
+    # ---- (2b) the exchange step alone (packed-gradient all-reduce), for the scaling analysis ----
+    allreduce_ms = None
+    if world > 1:
+        def only_reduce():
+            return refine.reduce_gradients(state.grad, torch.zeros((), device=dev), group)
+        allreduce_ms, _ = timed(only_reduce, 10, 3)
 
     # ---- (3) end to end: host buffers in, loss out ----
     e2e = None
@@ -387,13 +439,33 @@ def main():
         "data": "synthetic", "config": workload_config(args, cfg), "e2e": e2e, "gpu_launches": int(launches),
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "fwd_mpix_s": fwd_mpix, "fwd_ms": ms_fwd, "loss": loss_val, "loss_impl": loss_impl,
-        "num_rendered_rank0": int(R_local), "stages": stage_report, "ref_cuda": ref_cuda,
+        "num_rendered_rank0": int(R_local), "allreduce_ms": allreduce_ms,
+        "allreduce_bytes": int(state.grad.numel() * 4), "per_rank": per_rank, "view_assignment": assignment, "stages": stage_report, "ref_cuda": ref_cuda,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     return 0
+
+
+def measure_view_costs(cfg, cams, sc, dev):
+    """Instances R_v of each view (forward only, one view at a time) — the cost proxy for view balancing."""
+    import torch
+    from igs_b200 import scenes
+    import igs_b200
+    scales, rot, opac = scenes.activated(sc)
+    t = [x.to(dev) for x in (sc.xyz, opac, scales, rot, sc.sh)]
+    bg = torch.zeros(3, device=dev)
+    e = torch.Tensor([])
+    costs = []
+    for v in range(cfg["V"]):
+        out = igs_b200._C.rasterize_gaussians(bg, t[0], e, t[1], t[2], t[3], 1.0, e, cams.viewmatrix[v].to(dev).contiguous(),
+                                              cams.projmatrix[v].to(dev).contiguous(), cams.tanfovx, cams.tanfovy, 0.0,
+                                              cfg["H"], cfg["W"], t[4], 3, cams.campos[v].to(dev).contiguous(), False, False,
+                                              False, False)
+        costs.append(int(out[0]))
+    return costs
 
 
 def time_reference_cuda(cfg, cams, sc, gt_dev, dev, loss_impl="torch", steps=3):

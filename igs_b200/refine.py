@@ -211,6 +211,20 @@ def pack_gradients(grads: dict, P: int) -> torch.Tensor:
     return torch.cat([grads[n].reshape(P * k) for n, k in GROUPS])
 
 
+def shard_views_balanced(costs, rank: int, world: int):
+    """Longest-processing-time-first packing of views onto ranks by a per-view cost (e.g. instance counts of the
+    previous iteration); deterministic, so every rank derives the same assignment.  Pixel work is equal per view,
+    so each view's cost gets a constant pixel term added by the caller if wanted."""
+    order = sorted(range(len(costs)), key=lambda v: (-costs[v], v))
+    load = [0.0] * world
+    mine = [[] for _ in range(world)]
+    for v in order:
+        r = min(range(world), key=lambda i: (load[i], i))
+        load[r] += float(costs[v])
+        mine[r].append(v)
+    return sorted(mine[rank])
+
+
 def shard_views(total_views: int, rank: int, world: int):
     """View v -> rank v mod world: 20 views on 8 ranks = 3,3,3,3,2,2,2,2."""
     return list(range(rank, total_views, world))

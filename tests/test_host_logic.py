@@ -59,6 +59,16 @@ def test_shard_views():
     assert shard_views(3, 5, 8) == []
 
 
+def test_shard_views_balanced():
+    from igs_b200.refine import shard_views_balanced
+    costs = [10, 9, 8, 7, 6, 5, 4, 3, 2, 1]
+    parts = [shard_views_balanced(costs, r, 3) for r in range(3)]
+    assert sorted(v for p in parts for v in p) == list(range(10))
+    loads = [sum(costs[v] for v in p) for p in parts]
+    assert max(loads) - min(loads) <= 2
+    assert shard_views_balanced([5, 5], 2, 3) == []
+
+
 def test_scenes_are_deterministic_and_cameras_follow_reference_convention():
     from igs_b200 import scenes
     a, b = scenes.make_gaussians(100, 0), scenes.make_gaussians(100, 0)
