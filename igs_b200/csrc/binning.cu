@@ -111,12 +111,13 @@ __device__ __forceinline__ uint32_t digit_of(K key, int shift, uint32_t mask) {
   return (uint32_t)(key >> shift) & mask;
 }
 
-template <typename K>
+template <typename K, int BITS>
 __global__ void __launch_bounds__(IGS_SORT_THREADS)
 radix_hist_kernel(const K* __restrict__ keys, size_t n, int shift, uint32_t mask, uint32_t* __restrict__ hist,
                   unsigned nblocks) {
-  __shared__ uint32_t h[256];
-  h[threadIdx.x] = 0;
+  constexpr int NB = 1 << BITS;
+  __shared__ uint32_t h[NB];
+  for (int d = threadIdx.x; d < NB; d += IGS_SORT_THREADS) h[d] = 0;
   __syncthreads();
   size_t base = (size_t)blockIdx.x * IGS_SORT_TILE;
 #pragma unroll
@@ -125,23 +126,24 @@ radix_hist_kernel(const K* __restrict__ keys, size_t n, int shift, uint32_t mask
     if (i < n) atomicAdd(&h[digit_of<K>(keys[i], shift, mask)], 1u);
   }
   __syncthreads();
-  hist[(size_t)threadIdx.x * nblocks + blockIdx.x] = h[threadIdx.x];
+  for (int d = threadIdx.x; d < NB; d += IGS_SORT_THREADS) hist[(size_t)d * nblocks + blockIdx.x] = h[d];
 }
 
 // Each warp ranks a contiguous chunk of 512 keys in 16 rounds of 32 consecutive keys, so that the
 // rank order equals the index order (stability).
-template <typename K>
+template <typename K, int BITS>
 __global__ void __launch_bounds__(IGS_SORT_THREADS)
 radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, K* __restrict__ keys_out,
                      uint32_t* __restrict__ vals_out, size_t n, int shift, uint32_t mask,
                      const uint32_t* __restrict__ hist_scanned, unsigned nblocks) {
+  constexpr int NB = 1 << BITS;
   constexpr int WARPS = IGS_SORT_THREADS / 32;
   constexpr int CHUNK = IGS_SORT_TILE / WARPS;      // 512 keys per warp
   constexpr int ROUNDS = CHUNK / 32;                // 16
-  __shared__ uint32_t whist[WARPS][257];
+  __shared__ uint32_t whist[WARPS][NB + 1];
   const int w = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
-  for (int i = threadIdx.x; i < WARPS * 257; i += IGS_SORT_THREADS) (&whist[0][0])[i] = 0;
+  for (int i = threadIdx.x; i < WARPS * (NB + 1); i += IGS_SORT_THREADS) (&whist[0][0])[i] = 0;
   __syncthreads();
 
   const size_t wbase = (size_t)blockIdx.x * IGS_SORT_TILE + (size_t)w * CHUNK;
@@ -153,7 +155,7 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
     size_t i = wbase + (size_t)r * 32 + lane;
     bool valid = i < n;
     key[r] = valid ? keys_in[i] : K(0);
-    uint32_t d = valid ? digit_of<K>(key[r], shift, mask) : 256u;
+    uint32_t d = valid ? digit_of<K>(key[r], shift, mask) : (uint32_t)NB;
     dig[r] = d;
     uint32_t peers = __match_any_sync(0xffffffffu, d);
     uint32_t lt = peers & ((1u << lane) - 1u);
@@ -168,9 +170,8 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
     __syncwarp();
   }
   __syncthreads();
-  // cross-warp exclusive scan per digit; thread d owns digit d
-  {
-    uint32_t d = threadIdx.x;
+  // cross-warp exclusive scan per digit
+  for (uint32_t d = threadIdx.x; d < (uint32_t)NB; d += IGS_SORT_THREADS) {
     uint32_t run = hist_scanned[(size_t)d * nblocks + blockIdx.x];
 #pragma unroll
     for (int ww = 0; ww < WARPS; ww++) {
@@ -191,30 +192,36 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
   }
 }
 
+template <typename K, int BITS>
+static int radix_sort_passes(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint32_t* hist, cudaStream_t s) {
+  constexpr int NB = 1 << BITS;
+  unsigned nb = (unsigned)sort_blocks(n);
+  int cur = 0;
+  for (int shift = 0; shift < end_bit; shift += BITS) {
+    int bits = end_bit - shift < BITS ? end_bit - shift : BITS;
+    uint32_t mask = (1u << bits) - 1u;
+    count_launch(2);
+    radix_hist_kernel<K, BITS><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], n, shift, mask, hist, nb);
+    // in-place exclusive scan over the bin-major histogram (its block sums live behind the histogram)
+    launch_exclusive_scan(hist, hist, (size_t)NB * nb, hist + (size_t)NB * nb, nullptr, s);
+    radix_scatter_kernel<K, BITS><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
+                                                                  shift, mask, hist, nb);
+    cur ^= 1;
+  }
+  return cur;
+}
+
 // Sorts n (key,value) pairs on key bits [0, end_bit).  Buffers ping-pong; returns the index (0/1)
-// of the buffer pair that holds the sorted result.
+// of the buffer pair that holds the sorted result.  9-bit digits are used when they save a pass
+// (e.g. 17 tile-id bits at C3: 2 passes instead of 3).
 template <typename K>
 int radix_sort_pairs(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint32_t* hist,
                      uint32_t* scan_tmp_unused, cudaStream_t s) {
   (void)scan_tmp_unused;
   if (n == 0) return 0;
-  unsigned nb = (unsigned)sort_blocks(n);
-  int cur = 0;
-  // the scan of the [256][nb] histogram needs its own block-sum scratch; it lives behind the histogram
-  uint32_t* hsums = hist + (size_t)256 * nb;
-  (void)hsums;
-  for (int shift = 0; shift < end_bit; shift += 8) {
-    int bits = end_bit - shift < 8 ? end_bit - shift : 8;
-    uint32_t mask = (1u << bits) - 1u;
-    count_launch(2);
-    radix_hist_kernel<K><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], n, shift, mask, hist, nb);
-    // in-place exclusive scan over the bin-major histogram
-    launch_exclusive_scan(hist, hist, (size_t)256 * nb, hist + (size_t)256 * nb, nullptr, s);
-    radix_scatter_kernel<K><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
-                                                            shift, mask, hist, nb);
-    cur ^= 1;
-  }
-  return cur;
+  const int p8 = (end_bit + 7) / 8, p9 = (end_bit + 8) / 9;
+  if (p9 < p8) return radix_sort_passes<K, 9>(keys, vals, n, end_bit, hist, s);
+  return radix_sort_passes<K, 8>(keys, vals, n, end_bit, hist, s);
 }
 
 template int radix_sort_pairs<uint64_t>(uint64_t* keys[2], uint32_t* vals[2], size_t, int, uint32_t*, uint32_t*, cudaStream_t);

@@ -99,10 +99,10 @@ __host__ __device__ inline size_t scan_blocks(size_t n) { return (n + 2047) / 20
 #define IGS_SORT_THREADS 256
 #define IGS_SORT_TILE (IGS_SORT_ITEMS * IGS_SORT_THREADS)
 __host__ __device__ inline size_t sort_blocks(size_t n) { return (n + IGS_SORT_TILE - 1) / IGS_SORT_TILE; }
-// u32 words needed for a [256][nblocks] radix histogram plus the block sums of its scan
+// u32 words needed for a [512][nblocks] radix histogram (9-bit digits) plus the block sums of its scan
 __host__ __device__ inline size_t radix_hist_words(size_t n) {
   size_t nb = sort_blocks(n ? n : 1);
-  return 256 * nb + scan_blocks(256 * nb) + 8;
+  return 512 * nb + scan_blocks(512 * nb) + 8;
 }
 
 __host__ __device__ inline GeomBuf carve_geom(char* base, size_t P, size_t V) {

@@ -73,6 +73,7 @@ struct GatherBwdParams {
   const int* radii;
   const uint32_t* tiles;
   const uint32_t* rank;
+  const uint32_t* sorted_gid;  // [V*P] depth-sorted position -> global Gaussian id
   const uint32_t* inst_off;
   const uint8_t* clamped;
   const float* grec;

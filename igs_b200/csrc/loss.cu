@@ -40,11 +40,25 @@ __device__ __forceinline__ float ld_pad(const float* __restrict__ p, int x, int 
   return (x >= 0 && x < W && y >= 0 && y < H) ? p[(size_t)y * W + x] : 0.0f;
 }
 
+// Register-tiled separable filter helpers.  Shared input tiles have a row stride of LOSS_TS floats (16-B aligned
+// rows); the horizontal pass gives each thread 4 adjacent output columns of one row (14 inputs, loaded as three
+// 16-B and one 8-B shared loads), the vertical pass gives each thread 4 adjacent output rows of one column
+// (14 inputs reused across the 4 outputs) — ~4x fewer shared-memory instructions than one output per thread.
+#define LOSS_TS 44
+
+__device__ __forceinline__ void load14(const float* row, float (&x)[14]) {
+  const float4 a = *reinterpret_cast<const float4*>(row), b = *reinterpret_cast<const float4*>(row + 4),
+               c = *reinterpret_cast<const float4*>(row + 8);
+  const float2 d = *reinterpret_cast<const float2*>(row + 12);
+  x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w; x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
+  x[8] = c.x; x[9] = c.y; x[10] = c.z; x[11] = c.w; x[12] = d.x; x[13] = d.y;
+}
+
 __global__ void __launch_bounds__(256)
 loss_pass1_kernel(LossParams p) {
-  __shared__ float sx[LOSS_TH][LOSS_TW + 1];
-  __shared__ float sy[LOSS_TH][LOSS_TW + 1];
-  __shared__ float hb[5][LOSS_TH][LOSS_BX + 1];
+  __shared__ __align__(16) float sx[LOSS_TH][LOSS_TS];
+  __shared__ __align__(16) float sy[LOSS_TH][LOSS_TS];
+  __shared__ __align__(16) float hb[5][LOSS_TH][LOSS_BX];
   __shared__ double red[8];
   const int plane = blockIdx.z;
   const float* __restrict__ X = p.pred + (size_t)plane * p.H * p.W;
@@ -57,47 +71,68 @@ loss_pass1_kernel(LossParams p) {
     sy[ty][tx] = ld_pad(Y, x0 + tx - LOSS_R, y0 + ty - LOSS_R, p.W, p.H);
   }
   __syncthreads();
-  // horizontal
-  for (int i = tid; i < LOSS_TH * LOSS_BX; i += 256) {
-    int ty = i / LOSS_BX, tx = i - ty * LOSS_BX;
-    float a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
+  // horizontal: task = (row r, column group cg of 4 outputs)
+  if (tid < LOSS_TH * (LOSS_BX / 4)) {
+    const int r = tid / (LOSS_BX / 4), cg = tid - r * (LOSS_BX / 4);
+    float xv[14], yv[14];
+    load14(&sx[r][cg * 4], xv);
+    load14(&sy[r][cg * 4], yv);
+    float o[5][4];
 #pragma unroll
-    for (int k = 0; k < 11; k++) {
-      float w = p.win[k], xv = sx[ty][tx + k], yv = sy[ty][tx + k];
-      a0 = fmaf(w, xv, a0); a1 = fmaf(w, yv, a1);
-      a2 = fmaf(w, xv * xv, a2); a3 = fmaf(w, yv * yv, a3); a4 = fmaf(w, xv * yv, a4);
+    for (int j = 0; j < 4; j++) {
+      float a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
+#pragma unroll
+      for (int k = 0; k < 11; k++) {
+        const float w = p.win[k], xx = xv[j + k], yy = yv[j + k];
+        a0 = fmaf(w, xx, a0); a1 = fmaf(w, yy, a1);
+        a2 = fmaf(w, xx * xx, a2); a3 = fmaf(w, yy * yy, a3); a4 = fmaf(w, xx * yy, a4);
+      }
+      o[0][j] = a0; o[1][j] = a1; o[2][j] = a2; o[3][j] = a3; o[4][j] = a4;
     }
-    hb[0][ty][tx] = a0; hb[1][ty][tx] = a1; hb[2][ty][tx] = a2; hb[3][ty][tx] = a3; hb[4][ty][tx] = a4;
+#pragma unroll
+    for (int q = 0; q < 5; q++)
+      *reinterpret_cast<float4*>(&hb[q][r][cg * 4]) = make_float4(o[q][0], o[q][1], o[q][2], o[q][3]);
   }
   __syncthreads();
-  // vertical + SSIM + partials
+  // vertical + SSIM + partials: task = (column c, row group rg of 4 outputs)
   double acc = 0.0;
   const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-  for (int i = tid; i < LOSS_BY * LOSS_BX; i += 256) {
-    int ty = i / LOSS_BX, tx = i - ty * LOSS_BX;
-    int gx = x0 + tx, gy = y0 + ty;
-    if (gx >= p.W || gy >= p.H) continue;
-    float mu1 = 0, mu2 = 0, e11 = 0, e22 = 0, e12 = 0;
+  if (tid < LOSS_BX * (LOSS_BY / 4)) {
+    const int c = tid % LOSS_BX, rg = tid / LOSS_BX;
+    float m[5][4];
 #pragma unroll
-    for (int k = 0; k < 11; k++) {
-      float w = p.win[k];
-      mu1 = fmaf(w, hb[0][ty + k][tx], mu1); mu2 = fmaf(w, hb[1][ty + k][tx], mu2);
-      e11 = fmaf(w, hb[2][ty + k][tx], e11); e22 = fmaf(w, hb[3][ty + k][tx], e22);
-      e12 = fmaf(w, hb[4][ty + k][tx], e12);
+    for (int q = 0; q < 5; q++) {
+      float in[14];
+#pragma unroll
+      for (int k = 0; k < 14; k++) in[k] = hb[q][rg * 4 + k][c];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        float a = 0;
+#pragma unroll
+        for (int k = 0; k < 11; k++) a = fmaf(p.win[k], in[j + k], a);
+        m[q][j] = a;
+      }
     }
-    float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
-    float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
-    float A = 2.0f * mu12 + C1, B = 2.0f * s12 + C2, Cc = mu1_sq + mu2_sq + C1, D = s1 + s2 + C2;
-    float inv = 1.0f / (Cc * D);
-    float ssim = A * B * inv;
-    // partials of ssim w.r.t. mu1 (E's held fixed), E11, E12
-    float dmu1 = (2.0f * mu2 * B - 2.0f * mu2 * A) * inv - ssim * (2.0f * mu1 * D - 2.0f * mu1 * Cc) * inv;
-    float d11 = -ssim / D;
-    float d12 = 2.0f * A * inv;
-    size_t o = (size_t)plane * p.H * p.W + (size_t)gy * p.W + gx;
-    p.dmu1[o] = dmu1; p.dE11[o] = d11; p.dE12[o] = d12;
-    float xv = sx[ty + LOSS_R][tx + LOSS_R], yv = sy[ty + LOSS_R][tx + LOSS_R];
-    acc += (double)(p.lambda * fabsf(xv - yv)) - (double)((1.0f - p.lambda) * ssim);
+    const int gx = x0 + c;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int gy = y0 + rg * 4 + j;
+      if (gx >= p.W || gy >= p.H) continue;
+      const float mu1 = m[0][j], mu2 = m[1][j], e11 = m[2][j], e22 = m[3][j], e12 = m[4][j];
+      const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
+      const float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
+      const float A = 2.0f * mu12 + C1, B = 2.0f * s12 + C2, Cc = mu1_sq + mu2_sq + C1, D = s1 + s2 + C2;
+      const float inv = 1.0f / (Cc * D);
+      const float ssim = A * B * inv;
+      // partials of ssim w.r.t. mu1 (E's held fixed), E11, E12
+      const float dmu1 = (2.0f * mu2 * B - 2.0f * mu2 * A) * inv - ssim * (2.0f * mu1 * D - 2.0f * mu1 * Cc) * inv;
+      const float d11 = -ssim / D;
+      const float d12 = 2.0f * A * inv;
+      const size_t o = (size_t)plane * p.H * p.W + (size_t)gy * p.W + gx;
+      p.dmu1[o] = dmu1; p.dE11[o] = d11; p.dE12[o] = d12;
+      const float xv = sx[rg * 4 + j + LOSS_R][c + LOSS_R], yv = sy[rg * 4 + j + LOSS_R][c + LOSS_R];
+      acc += (double)(p.lambda * fabsf(xv - yv)) - (double)((1.0f - p.lambda) * ssim);
+    }
   }
   // block reduce (fixed order)
 #pragma unroll
@@ -113,10 +148,10 @@ loss_pass1_kernel(LossParams p) {
 
 __global__ void __launch_bounds__(256)
 loss_pass2_kernel(LossParams p) {
-  __shared__ float s0[LOSS_TH][LOSS_TW + 1];
-  __shared__ float s1[LOSS_TH][LOSS_TW + 1];
-  __shared__ float s2[LOSS_TH][LOSS_TW + 1];
-  __shared__ float hb[3][LOSS_TH][LOSS_BX + 1];
+  __shared__ __align__(16) float s0[LOSS_TH][LOSS_TS];
+  __shared__ __align__(16) float s1[LOSS_TH][LOSS_TS];
+  __shared__ __align__(16) float s2[LOSS_TH][LOSS_TS];
+  __shared__ __align__(16) float hb[3][LOSS_TH][LOSS_BX];
   const int plane = blockIdx.z;
   const size_t po = (size_t)plane * p.H * p.W;
   const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
@@ -129,33 +164,56 @@ loss_pass2_kernel(LossParams p) {
     s2[ty][tx] = ld_pad(p.dE12 + po, gx, gy, p.W, p.H);
   }
   __syncthreads();
-  for (int i = tid; i < LOSS_TH * LOSS_BX; i += 256) {
-    int ty = i / LOSS_BX, tx = i - ty * LOSS_BX;
-    float a0 = 0, a1 = 0, a2 = 0;
+  if (tid < LOSS_TH * (LOSS_BX / 4)) {
+    const int r = tid / (LOSS_BX / 4), cg = tid - r * (LOSS_BX / 4);
+    float v0[14], v1[14], v2[14];
+    load14(&s0[r][cg * 4], v0);
+    load14(&s1[r][cg * 4], v1);
+    load14(&s2[r][cg * 4], v2);
+    float o[3][4];
 #pragma unroll
-    for (int k = 0; k < 11; k++) {
-      float w = p.win[k];
-      a0 = fmaf(w, s0[ty][tx + k], a0); a1 = fmaf(w, s1[ty][tx + k], a1); a2 = fmaf(w, s2[ty][tx + k], a2);
+    for (int j = 0; j < 4; j++) {
+      float a0 = 0, a1 = 0, a2 = 0;
+#pragma unroll
+      for (int k = 0; k < 11; k++) {
+        const float w = p.win[k];
+        a0 = fmaf(w, v0[j + k], a0); a1 = fmaf(w, v1[j + k], a1); a2 = fmaf(w, v2[j + k], a2);
+      }
+      o[0][j] = a0; o[1][j] = a1; o[2][j] = a2;
     }
-    hb[0][ty][tx] = a0; hb[1][ty][tx] = a1; hb[2][ty][tx] = a2;
+#pragma unroll
+    for (int q = 0; q < 3; q++)
+      *reinterpret_cast<float4*>(&hb[q][r][cg * 4]) = make_float4(o[q][0], o[q][1], o[q][2], o[q][3]);
   }
   __syncthreads();
-  for (int i = tid; i < LOSS_BY * LOSS_BX; i += 256) {
-    int ty = i / LOSS_BX, tx = i - ty * LOSS_BX;
-    int gx = x0 + tx, gy = y0 + ty;
-    if (gx >= p.W || gy >= p.H) continue;
-    float c0 = 0, c1 = 0, c2 = 0;
+  if (tid < LOSS_BX * (LOSS_BY / 4)) {
+    const int c = tid % LOSS_BX, rg = tid / LOSS_BX;
+    float m[3][4];
 #pragma unroll
-    for (int k = 0; k < 11; k++) {
-      float w = p.win[k];
-      c0 = fmaf(w, hb[0][ty + k][tx], c0); c1 = fmaf(w, hb[1][ty + k][tx], c1); c2 = fmaf(w, hb[2][ty + k][tx], c2);
+    for (int q = 0; q < 3; q++) {
+      float in[14];
+#pragma unroll
+      for (int k = 0; k < 14; k++) in[k] = hb[q][rg * 4 + k][c];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        float a = 0;
+#pragma unroll
+        for (int k = 0; k < 11; k++) a = fmaf(p.win[k], in[j + k], a);
+        m[q][j] = a;
+      }
     }
-    size_t o = po + (size_t)gy * p.W + gx;
-    float xv = p.pred[o], yv = p.gt[o];
-    float dssim = c0 + 2.0f * xv * c1 + yv * c2;
-    float d = xv - yv;
-    float sgn = (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f);   // torch: sign(0) = 0
-    p.dpred[o] = (p.lambda * sgn - (1.0f - p.lambda) * dssim) * p.inv_n;
+    const int gx = x0 + c;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int gy = y0 + rg * 4 + j;
+      if (gx >= p.W || gy >= p.H) continue;
+      const size_t o = po + (size_t)gy * p.W + gx;
+      const float xv = p.pred[o], yv = p.gt[o];
+      const float dssim = m[0][j] + 2.0f * xv * m[1][j] + yv * m[2][j];
+      const float d = xv - yv;
+      const float sgn = (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f);   // torch: sign(0) = 0
+      p.dpred[o] = (p.lambda * sgn - (1.0f - p.lambda) * dssim) * p.inv_n;
+    }
   }
 }
 

@@ -2,7 +2,7 @@
 // (DGR/cuda_rasterizer/backward.cu:145-488) and backward preprocessCUDA (:560-628, SH :21-140,
 // cov3D :492-555).
 //
-//   gather_bwd_kernel : one thread per (view, Gaussian).  Sums the dense per-instance records that
+//   gather_bwd_kernel : one thread per (view, Gaussian), in depth-sorted order.  Sums the dense per-instance records that
 //                       blend_bwd wrote for this Gaussian's consecutive emission slots (this replaces
 //                       the reference's 25 atomics per pixel pair), then runs the view-dependent
 //                       chain: conic/coef -> cov2D -> (cov3D, mean), plane/normal -> (Vrk, mean),
@@ -28,10 +28,13 @@ namespace igs {
 
 __global__ void __launch_bounds__(128)
 gather_bwd_kernel(GatherBwdParams p) {
-  int g = blockIdx.x * blockDim.x + threadIdx.x;
-  int v = blockIdx.y;
-  if (g >= p.P) return;
-  size_t gid = (size_t)v * p.P + g;
+  // Threads are indexed by DEPTH-SORTED position: emission slots of neighbouring positions are adjacent in grec, so
+  // the record reads of a warp fall into one contiguous region (the small per-Gaussian inputs become the gathers).
+  const size_t pos = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (pos >= (size_t)p.V * p.P) return;
+  const size_t gid = p.sorted_gid[pos];
+  const int v = (int)(gid / (size_t)p.P);
+  const int g = (int)(gid - (size_t)v * p.P);
   float4* part = reinterpret_cast<float4*>(p.partial + gid * 16);
   float* dm2 = p.dL_dmeans2D + gid * 3;
   if (!(p.radii[gid] > 0)) {
@@ -44,8 +47,8 @@ gather_bwd_kernel(GatherBwdParams p) {
 #pragma unroll
   for (int i = 0; i < 25; i++) s[i] = 0.0f;
   {
-    uint32_t off = p.inst_off[p.rank[gid]];
-    uint32_t n = p.tiles[gid];
+    const uint32_t off = p.inst_off[pos];
+    const uint32_t n = p.inst_off[pos + 1] - off;
     if (p.ns == 16) {
       const float4* r = reinterpret_cast<const float4*>(p.grec + (size_t)off * 16);
       for (uint32_t k = 0; k < n; k++) {
@@ -485,9 +488,9 @@ finish_bwd_kernel(FinishBwdParams p) {
 
 void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s) {
   if (p.P <= 0) return;
-  dim3 grid((p.P + 127) / 128, p.V);
+  const size_t VP = (size_t)p.V * p.P;
   count_launch();
-  gather_bwd_kernel<<<grid, 128, 0, s>>>(p);
+  gather_bwd_kernel<<<(unsigned)((VP + 127) / 128), 128, 0, s>>>(p);
 }
 
 void launch_finish_bwd(const FinishBwdParams& p, cudaStream_t s) {
