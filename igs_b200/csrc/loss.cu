@@ -65,10 +65,17 @@ loss_pass1_kernel(LossParams p) {
   const float* __restrict__ Y = p.gt + (size_t)plane * p.H * p.W;
   const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
   const int tid = threadIdx.x;
-  for (int i = tid; i < LOSS_TH * LOSS_TW; i += 256) {
-    int ty = i / LOSS_TW, tx = i - ty * LOSS_TW;
-    sx[ty][tx] = ld_pad(X, x0 + tx - LOSS_R, y0 + ty - LOSS_R, p.W, p.H);
-    sy[ty][tx] = ld_pad(Y, x0 + tx - LOSS_R, y0 + ty - LOSS_R, p.W, p.H);
+  // tile + halo, one row per warp iteration (no index division; zero padding outside the image)
+  for (int ty = tid >> 5; ty < LOSS_TH; ty += 8) {
+    const int gy = y0 + ty - LOSS_R;
+    const bool rowok = gy >= 0 && gy < p.H;
+    const size_t ro = (size_t)(rowok ? gy : 0) * p.W;
+    for (int tx = tid & 31; tx < LOSS_TW; tx += 32) {
+      const int gx = x0 + tx - LOSS_R;
+      const bool ok = rowok && gx >= 0 && gx < p.W;
+      sx[ty][tx] = ok ? X[ro + gx] : 0.0f;
+      sy[ty][tx] = ok ? Y[ro + gx] : 0.0f;
+    }
   }
   __syncthreads();
   // horizontal: task = (row r, column group cg of 4 outputs)
@@ -156,12 +163,17 @@ loss_pass2_kernel(LossParams p) {
   const size_t po = (size_t)plane * p.H * p.W;
   const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
   const int tid = threadIdx.x;
-  for (int i = tid; i < LOSS_TH * LOSS_TW; i += 256) {
-    int ty = i / LOSS_TW, tx = i - ty * LOSS_TW;
-    int gx = x0 + tx - LOSS_R, gy = y0 + ty - LOSS_R;
-    s0[ty][tx] = ld_pad(p.dmu1 + po, gx, gy, p.W, p.H);
-    s1[ty][tx] = ld_pad(p.dE11 + po, gx, gy, p.W, p.H);
-    s2[ty][tx] = ld_pad(p.dE12 + po, gx, gy, p.W, p.H);
+  for (int ty = tid >> 5; ty < LOSS_TH; ty += 8) {
+    const int gy = y0 + ty - LOSS_R;
+    const bool rowok = gy >= 0 && gy < p.H;
+    const size_t ro = po + (size_t)(rowok ? gy : 0) * p.W;
+    for (int tx = tid & 31; tx < LOSS_TW; tx += 32) {
+      const int gx = x0 + tx - LOSS_R;
+      const bool ok = rowok && gx >= 0 && gx < p.W;
+      s0[ty][tx] = ok ? p.dmu1[ro + gx] : 0.0f;
+      s1[ty][tx] = ok ? p.dE11[ro + gx] : 0.0f;
+      s2[ty][tx] = ok ? p.dE12[ro + gx] : 0.0f;
+    }
   }
   __syncthreads();
   if (tid < LOSS_TH * (LOSS_BX / 4)) {
