@@ -348,6 +348,7 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   if (R > 0) {
     BlendBwdParams bp;
     bp.W = W; bp.H = H; bp.tiles_x = tiles_x; bp.tiles_y = tiles_y; bp.focal_x = focal_x; bp.focal_y = focal_y;
+    bp.half_w = 0.5f * W; bp.half_h = 0.5f * H;
     bp.ranges = I.ranges; bp.point_list = B.point_list; bp.point_e = B.tval[bcur]; bp.head = G.head; bp.tail = G.tail;
     bp.bg = a->background; bp.alphas = a->alphas; bp.normalmap = a->normalmap; bp.n_contrib = I.n_contrib;
     bp.accum_coord = I.accum_coord; bp.accum_depth = I.accum_depth; bp.normal_length = I.normal_length;

@@ -19,6 +19,7 @@
 //     every omitted term is multiplied by an exactly-zero cotangent in the reference.
 #include "common.cuh"
 #include "blend_common.cuh"
+#include <cstdlib>
 #include "kernels.cuh"
 
 namespace igs {
@@ -49,12 +50,15 @@ __device__ __forceinline__ void warp_reduce_scatter(float (&v)[NS], int lane) {
   }
 }
 
-template <bool COORD, bool DEPTH, bool NORMAL, bool GEOGRAD>
-__global__ void __launch_bounds__(256)
+// instances staged per round: sized so that MINB CTAs fit the SM's shared memory
+__host__ __device__ constexpr int bwd_batch(bool geograd, int minb) { return geograd ? 64 : (minb >= 4 ? 96 : 128); }
+
+template <bool COORD, bool DEPTH, bool NORMAL, bool GEOGRAD, int MINB>
+__global__ void __launch_bounds__(256, MINB)
 blend_bwd_kernel(BlendBwdParams p) {
   constexpr int NS = GEOGRAD ? 32 : 16;         // floats per gradient record in global memory
   constexpr int NV = GEOGRAD ? 25 : 10;         // values actually produced per pair
-  constexpr int BATCH = GEOGRAD ? 64 : 128;     // instances staged per round
+  constexpr int BATCH = bwd_batch(GEOGRAD, MINB);
   constexpr bool GEO = GEOGRAD && (COORD || DEPTH || NORMAL);
   // survivors: [0,B) head.a {x, y, conic.x, conic.y}; [B,2B) head.b {conic.z, opacity, r, g};
   // [2B,3B) {blue, list position (bits), tau, batch slot (bits)}
@@ -69,6 +73,7 @@ blend_bwd_kernel(BlendBwdParams p) {
   extern __shared__ float s_acc[];
   // colour-only path: per-warp [10][36] transpose staging for the cross-pixel reduction (columns 32..35 stay zero)
   __shared__ __align__(16) float s_stage[GEOGRAD ? 4 : 8 * 10 * 36];
+  __shared__ float s_dummy[GEOGRAD ? 1 : 256];  // sink for the lanes that own no value in the reduction
 
   const int tiles = p.tiles_x * p.tiles_y;
   const int gt = blockIdx.x;
@@ -100,7 +105,11 @@ blend_bwd_kernel(BlendBwdParams p) {
   // reduction role of this lane in the colour-only path: value rv = lane / 3, segment rs = lane % 3 (12 pixels each)
   const uint32_t rv = (uint32_t)lane / 3u, rs = (uint32_t)lane - rv * 3u;
   const uint32_t stage_wr = stage_base + (uint32_t)lane * 4;
-  const uint32_t stage_rd = stage_base + (rv * 36 + rs * 12) * 4;
+  const bool red_owner = (rs == 0u) && (lane < 30);
+  const uint32_t stage_rd = stage_base + (lane < 30 ? (rv * 36 + rs * 12) * 4 : 0u);  // lanes 30, 31: any valid row
+  // accumulator address of this lane for batch slot s is red_base + s * red_mul (non-owners hit their dummy word)
+  const uint32_t red_base = red_owner ? acc_base + rv * 4 : smem_addr(s_dummy) + threadIdx.x * 4;
+  const uint32_t red_mul = red_owner ? (uint32_t)(NV * 4) : 0u;
 
   const uint2 range = p.ranges[gt];
   const uint32_t last_contributor = inside ? p.n_contrib[(size_t)v * 2 * N + pix_id] : 0u;
@@ -180,7 +189,6 @@ blend_bwd_kernel(BlendBwdParams p) {
     }
   }
   const float bg_dot_dpixel = p.bg[0] * dLp0 + p.bg[1] * dLp1 + p.bg[2] * dLp2;
-  const float ddelx_dx = 0.5f * p.W, ddely_dy = 0.5f * p.H;
 
   float last_alpha = 0, accum_alpha_rec = 0;
   float ar0 = 0, ar1 = 0, ar2 = 0, lc0 = 0, lc1 = 0, lc2 = 0;      // colour recurrence
@@ -323,9 +331,14 @@ blend_bwd_kernel(BlendBwdParams p) {
           const float dG_ddelx = -gdx * a.z - gdy * a.w;
           const float dG_ddely = -gdy * bq.x - gdx * a.w;
           const float ax = dL_dG * dG_ddelx, ay = dL_dG * dG_ddely;
-          val[3] = (ax + dL_ddelx_geo) * ddelx_dx;
-          val[4] = (ay + dL_ddely_geo) * ddely_dy;
-          val[5] = fabsf(ax * ddelx_dx) + fabsf(ay * ddely_dy);
+          if constexpr (GEO) {
+            val[3] = (ax + dL_ddelx_geo) * p.half_w;
+            val[4] = (ay + dL_ddely_geo) * p.half_h;
+          } else {
+            val[3] = ax * p.half_w;
+            val[4] = ay * p.half_h;
+          }
+          val[5] = fabsf(ax * p.half_w) + fabsf(ay * p.half_h);
           val[6] = -0.5f * gdx * dx * dL_dG;
           val[7] = -0.5f * gdx * dy * dL_dG;
           val[8] = -0.5f * gdy * dy * dL_dG;
@@ -345,16 +358,11 @@ blend_bwd_kernel(BlendBwdParams p) {
           sts32<6 * 144>(stage_wr, val[6]); sts32<7 * 144>(stage_wr, val[7]); sts32<8 * 144>(stage_wr, val[8]);
           sts32<9 * 144>(stage_wr, val[9]);
           __syncwarp();
-          float sum = 0.0f;
-          if (lane < 30) {
-            const float4 x0 = lds128<0>(stage_rd), x1 = lds128<16>(stage_rd), x2 = lds128<32>(stage_rd);
-            sum = ((x0.x + x0.y) + (x0.z + x0.w)) + ((x1.x + x1.y) + (x1.z + x1.w)) + ((x2.x + x2.y) + (x2.z + x2.w));
-          }
+          const float4 x0 = lds128<0>(stage_rd), x1 = lds128<16>(stage_rd), x2 = lds128<32>(stage_rd);
+          float sum = ((x0.x + x0.y) + (x0.z + x0.w)) + ((x1.x + x1.y) + (x1.z + x1.w)) + ((x2.x + x2.y) + (x2.z + x2.w));
           sum += __shfl_down_sync(0xffffffffu, sum, 1) + __shfl_down_sync(0xffffffffu, sum, 2);
-          if (rs == 0 && lane < 30) {
-            const uint32_t aa = acc_base + (__float_as_uint(cq.w) * NV + rv) * 4;
-            sts32<0>(aa, lds32<0>(aa) + sum);
-          }
+          const uint32_t aa = red_base + __float_as_uint(cq.w) * red_mul;
+          sts32<0>(aa, lds32<0>(aa) + sum);
           __syncwarp();
         }
       }
@@ -381,22 +389,26 @@ blend_bwd_kernel(BlendBwdParams p) {
 
 int blend_bwd_record_floats(bool geograd) { return geograd ? 32 : 16; }
 
-template <bool C, bool D, bool N, bool G>
+template <bool C, bool D, bool N, bool G, int MINB>
 static void launch_one(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
-  constexpr int bytes = 8 * (G ? 64 : 128) * (G ? 25 : 10) * 4;  // per-warp accumulators (dynamic shared memory)
+  constexpr int bytes = 8 * bwd_batch(G, MINB) * (G ? 25 : 10) * 4;  // per-warp accumulators (dynamic shared memory)
   // > 48 KB of dynamic shared memory needs the opt-in; it is per device, so it is (cheaply) set on every launch
-  cudaFuncSetAttribute(blend_bwd_kernel<C, D, N, G>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  blend_bwd_kernel<C, D, N, G><<<nblocks, 256, bytes, s>>>(p);
+  cudaFuncSetAttribute(blend_bwd_kernel<C, D, N, G, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  blend_bwd_kernel<C, D, N, G, MINB><<<nblocks, 256, bytes, s>>>(p);
 }
 
 void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s) {
   int nblocks = V * p.tiles_x * p.tiles_y;
   if (nblocks <= 0) return;
   count_launch();
-  if (!geograd || (!coord && !depth)) launch_one<false, false, false, false>(p, nblocks, s);
-  else if (coord && depth) launch_one<true, true, true, true>(p, nblocks, s);
-  else if (coord) launch_one<true, false, true, true>(p, nblocks, s);
-  else launch_one<false, true, true, true>(p, nblocks, s);
+  // IGS_BWD_OCC=4 selects the 64-register / 96-instance-batch build of the colour-only kernel (4 CTAs/SM)
+  static const int occ = [] { const char* e = getenv("IGS_BWD_OCC"); return e ? atoi(e) : 4; }();
+  if (!geograd || (!coord && !depth)) {
+    if (occ >= 4) launch_one<false, false, false, false, 4>(p, nblocks, s);
+    else launch_one<false, false, false, false, 3>(p, nblocks, s);
+  } else if (coord && depth) launch_one<true, true, true, true, 2>(p, nblocks, s);
+  else if (coord) launch_one<true, false, true, true, 2>(p, nblocks, s);
+  else launch_one<false, true, true, true, 2>(p, nblocks, s);
 }
 
 }  // namespace igs

@@ -14,14 +14,15 @@
 // compiled operation order (common.cuh splat_power; expf, not __expf), so n_contrib is bit-exact.
 #include "common.cuh"
 #include "blend_common.cuh"
+#include <cstdlib>
 #include "kernels.cuh"
 
 namespace igs {
 
 #define BLEND_BATCH 256
 
-template <bool COORD, bool DEPTH, bool NORMAL>
-__global__ void __launch_bounds__(256)
+template <bool COORD, bool DEPTH, bool NORMAL, int MINB>
+__global__ void __launch_bounds__(256, MINB)
 blend_fwd_kernel(BlendFwdParams p) {
   constexpr bool GEO = COORD || DEPTH || NORMAL;
   // survivors of the current batch: [0,256) head.a {x, y, conic.x, conic.y}; [256,512) head.b {conic.z, opacity, r, g};
@@ -216,10 +217,19 @@ void launch_blend_fwd(const BlendFwdParams& p, int V, bool coord, bool depth, cu
   int nblocks = V * p.tiles_x * p.tiles_y;
   if (nblocks <= 0) return;
   count_launch();
-  if (coord && depth) blend_fwd_kernel<true, true, true><<<nblocks, 256, 0, s>>>(p);
-  else if (coord && !depth) blend_fwd_kernel<true, false, true><<<nblocks, 256, 0, s>>>(p);
-  else if (!coord && depth) blend_fwd_kernel<false, true, true><<<nblocks, 256, 0, s>>>(p);
-  else blend_fwd_kernel<false, false, false><<<nblocks, 256, 0, s>>>(p);
+  // 64-register build, 4 CTAs/SM (measured 10% faster than the spill-free 3 CTAs/SM build, IGS_FWD_OCC=3)
+  static const int occ = [] { const char* e = getenv("IGS_FWD_OCC"); return e ? atoi(e) : 4; }();
+  if (occ >= 4) {
+    if (coord && depth) blend_fwd_kernel<true, true, true, 4><<<nblocks, 256, 0, s>>>(p);
+    else if (coord && !depth) blend_fwd_kernel<true, false, true, 4><<<nblocks, 256, 0, s>>>(p);
+    else if (!coord && depth) blend_fwd_kernel<false, true, true, 4><<<nblocks, 256, 0, s>>>(p);
+    else blend_fwd_kernel<false, false, false, 4><<<nblocks, 256, 0, s>>>(p);
+  } else {
+    if (coord && depth) blend_fwd_kernel<true, true, true, 3><<<nblocks, 256, 0, s>>>(p);
+    else if (coord && !depth) blend_fwd_kernel<true, false, true, 3><<<nblocks, 256, 0, s>>>(p);
+    else if (!coord && depth) blend_fwd_kernel<false, true, true, 3><<<nblocks, 256, 0, s>>>(p);
+    else blend_fwd_kernel<false, false, false, 3><<<nblocks, 256, 0, s>>>(p);
+  }
 }
 
 }  // namespace igs

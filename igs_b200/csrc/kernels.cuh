@@ -39,6 +39,7 @@ struct BlendFwdParams {
 struct BlendBwdParams {
   int W, H, tiles_x, tiles_y;
   float focal_x, focal_y;
+  float half_w, half_h;  // 0.5*W, 0.5*H (d ndc->pixel), kept in the constant bank
   const uint2* ranges;
   const uint32_t* point_list;
   const uint32_t* point_e;
