@@ -386,6 +386,9 @@ def main():
     stage_ms = {n: (ms, c) for n, ms, c in stages if c > 0}
     VP = Vl * P
     R = R_local
+    # tile-id sort: 8-bit digits, or 9-bit when that saves a pass (binning.cu radix_sort_pairs)
+    tile_bits = max(1, (max(1, Vl) * ((W + 15) // 16) * ((H + 15) // 16) - 1).bit_length())
+    sort_passes = min((tile_bits + 7) // 8, (tile_bits + 8) // 9)
     # algorithmic bytes per launch of each stage for THIS design
     alg = {
         "gauss_setup": P * (28 + 24 + 96),
@@ -393,7 +396,7 @@ def main():
         "depth_sort": 5 * VP * (12 + 12) + 5 * VP * 8,
         "scan_rank": VP * (4 + 4 + 4 + 4) + VP * 8,
         "emit": VP * (4 + 8 + 32 + 4) + R * 12,
-        "tile_sort": 3 * R * (8 + 8) + 3 * R * 4,
+        "tile_sort": sort_passes * R * (8 + 8) + sort_passes * R * 4,
         "finalize_bins": R * (4 + 4 + 4 + 4),
         "blend_fwd": R * (4 + 32 + 64) + Vl * N * 88,
         "blend_bwd": R * (4 + 4 + 32 + 4) + Vl * N * (12 + 4 + 8) + R * 64,
@@ -401,6 +404,7 @@ def main():
         "finish_bwd": VP * 64 + P * (12 + 192 + 12 + 16 + 12 + 4 + 24 + 192 + 12 + 16),
         "adam": P * 59 * 4 * 7,
         "loss": Vl * N * 3 * 4 * 3,
+        "activate": P * 80,   # mean of the forward (64 B/Gaussian) and backward (96 B/Gaussian) launches
     }
     top = max(stage_ms.items(), key=lambda kv: kv[1][0])[0] if stage_ms else None
     roofline = None

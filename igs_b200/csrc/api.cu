@@ -29,7 +29,7 @@ void set_error(const char* fmt, ...) {
 // resolved lazily in igs_stage_timing_read() so that no synchronisation is added to the timed path.
 static const char* const kStageNames[IGS_NUM_STAGES] = {
     "gauss_setup", "project", "depth_sort", "scan_rank", "emit", "tile_sort", "finalize_bins", "blend_fwd",
-    "blend_bwd", "gather_bwd", "finish_bwd", "adam", "loss"};
+    "blend_bwd", "gather_bwd", "finish_bwd", "adam", "loss", "activate"};
 struct StageTimer {
   std::mutex mu;
   bool on = false;
@@ -129,8 +129,8 @@ extern "C" {
 
 const char* igs_last_error(void) { return igs::g_err; }
 int igs_abi_version(void) { return IGS_RASTER_ABI_VERSION; }
-int igs_refine_loss(const float* pred, const float* gt, int V, int height, int width, float lambda_l1, float* loss_sum,
-                    float* dL_dpred, igs_alloc_fn temp_alloc, void* temp_user, void* stream) {
+int igs_refine_loss(const float* pred, const float* gt, int V, int height, int width, float lambda_l1, float grad_scale,
+                    float* loss_sum, float* dL_dpred, igs_alloc_fn temp_alloc, void* temp_user, void* stream) {
   if (V < 0 || height <= 0 || width <= 0 || !temp_alloc) { set_error("bad argument"); return IGS_ERR_INVALID; }
   if (V == 0) return IGS_OK;
   if (!pred || !gt || !loss_sum || !dL_dpred) { set_error("null pointer"); return IGS_ERR_INVALID; }
@@ -140,7 +140,7 @@ int igs_refine_loss(const float* pred, const float* gt, int V, int height, int w
   tmp = (char*)(((uintptr_t)tmp + 255) & ~uintptr_t(255));
   {
     StageScope st(IGS_STAGE_LOSS, (cudaStream_t)stream);
-    launch_refine_loss(pred, gt, V, height, width, lambda_l1, loss_sum, dL_dpred, tmp, (cudaStream_t)stream);
+    launch_refine_loss(pred, gt, V, height, width, lambda_l1, grad_scale, loss_sum, dL_dpred, tmp, (cudaStream_t)stream);
   }
   IGS_CUDA_CHECK(cudaGetLastError());
   return IGS_OK;
@@ -443,6 +443,62 @@ int igs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
     StageScope st(IGS_STAGE_ADAM, (cudaStream_t)stream);
     adam_kernel<<<(unsigned)nb, 256, 0, (cudaStream_t)stream>>>(param, grad, exp_avg, exp_avg_sq, n, beta1, beta2, eps,
                                                                   step_size, inv_sqrt_bc2);
+  }
+  IGS_CUDA_CHECK(cudaGetLastError());
+  return IGS_OK;
+}
+
+int igs_adam_step_groups(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int ngroups,
+                         const size_t* sizes, const float* lrs, float beta1, float beta2, float eps, int step,
+                         void* stream) {
+  if (ngroups == 0) return IGS_OK;
+  if (ngroups < 0 || ngroups > 8 || !sizes || !lrs || !param || !grad || !exp_avg || !exp_avg_sq || step < 1) {
+    set_error("bad argument");
+    return IGS_ERR_INVALID;
+  }
+  const double bc1 = 1.0 - pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  float step_sizes[8];
+  for (int k = 0; k < ngroups; k++) step_sizes[k] = (float)((double)lrs[k] / bc1);
+  {
+    StageScope st(IGS_STAGE_ADAM, (cudaStream_t)stream);
+    launch_adam_groups(param, grad, exp_avg, exp_avg_sq, ngroups, sizes, step_sizes, beta1, beta2, eps,
+                       (float)(1.0 / sqrt(bc2)), (cudaStream_t)stream);
+  }
+  IGS_CUDA_CHECK(cudaGetLastError());
+  return IGS_OK;
+}
+
+int igs_activate_forward(int P, const float* log_scales, const float* raw_rot, const float* opacity_logit, float* scales,
+                         float* rotations, float* opacities, void* stream) {
+  if (P < 0) { set_error("bad argument"); return IGS_ERR_INVALID; }
+  if (P == 0) return IGS_OK;
+  if (!log_scales || !raw_rot || !opacity_logit || !scales || !rotations || !opacities) {
+    set_error("null pointer");
+    return IGS_ERR_INVALID;
+  }
+  {
+    StageScope st(IGS_STAGE_ACTIVATE, (cudaStream_t)stream);
+    launch_activate_fwd(P, log_scales, raw_rot, opacity_logit, scales, rotations, opacities, (cudaStream_t)stream);
+  }
+  IGS_CUDA_CHECK(cudaGetLastError());
+  return IGS_OK;
+}
+
+int igs_activate_backward(int P, const float* scales, const float* raw_rot, const float* opacities,
+                          const float* dL_dscales, const float* dL_drot, const float* dL_dopac, float* dL_dlog_scales,
+                          float* dL_draw_rot, float* dL_dlogit, void* stream) {
+  if (P < 0) { set_error("bad argument"); return IGS_ERR_INVALID; }
+  if (P == 0) return IGS_OK;
+  if (!scales || !raw_rot || !opacities || !dL_dscales || !dL_drot || !dL_dopac || !dL_dlog_scales || !dL_draw_rot ||
+      !dL_dlogit) {
+    set_error("null pointer");
+    return IGS_ERR_INVALID;
+  }
+  {
+    StageScope st(IGS_STAGE_ACTIVATE, (cudaStream_t)stream);
+    launch_activate_bwd(P, scales, raw_rot, opacities, dL_dscales, dL_drot, dL_dopac, dL_dlog_scales, dL_draw_rot,
+                        dL_dlogit, (cudaStream_t)stream);
   }
   IGS_CUDA_CHECK(cudaGetLastError());
   return IGS_OK;

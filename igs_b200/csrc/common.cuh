@@ -250,7 +250,7 @@ class StageScope {
 enum {
   IGS_STAGE_GAUSS_SETUP = 0, IGS_STAGE_PROJECT, IGS_STAGE_DEPTH_SORT, IGS_STAGE_SCAN_RANK, IGS_STAGE_EMIT,
   IGS_STAGE_TILE_SORT, IGS_STAGE_FINALIZE, IGS_STAGE_BLEND_FWD, IGS_STAGE_BLEND_BWD, IGS_STAGE_GATHER_BWD,
-  IGS_STAGE_FINISH_BWD, IGS_STAGE_ADAM, IGS_STAGE_LOSS, IGS_NUM_STAGES
+  IGS_STAGE_FINISH_BWD, IGS_STAGE_ADAM, IGS_STAGE_LOSS, IGS_STAGE_ACTIVATE, IGS_NUM_STAGES
 };
 #define IGS_CUDA_CHECK(expr)                                                      \
   do {                                                                            \

@@ -126,7 +126,14 @@ void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bo
 void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s);
 void launch_finish_bwd(const FinishBwdParams& p, cudaStream_t s);
 size_t refine_loss_scratch_bytes(int V, int H, int W);
-void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float* loss_sum,
+void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float grad_scale, float* loss_sum,
                         float* dpred, char* scratch, cudaStream_t s);
+void launch_activate_fwd(int P, const float* log_scales, const float* raw_rot, const float* logit, float* scales,
+                         float* rot, float* opac, cudaStream_t s);
+void launch_activate_bwd(int P, const float* scales, const float* raw_rot, const float* opac, const float* dL_dscales,
+                         const float* dL_drot, const float* dL_dopac, float* dL_dlog_scales, float* dL_draw_rot,
+                         float* dL_dlogit, cudaStream_t s);
+void launch_adam_groups(float* p, const float* g, float* m, float* v, int ngroups, const size_t* sizes,
+                        const float* step_sizes, float b1, float b2, float eps, float inv_sqrt_bc2, cudaStream_t s);
 
 }  // namespace igs

@@ -26,7 +26,7 @@ struct LossParams {
   int plane_per_view;      // 3
   float win[11];           // gauss(x) = exp(-(x-5)^2 / (2*1.5^2)) / sum, computed like loss_utils.py:23-25
   float lambda;
-  float inv_n;             // 1 / (3*H*W)
+  float inv_n;             // grad_scale / (3*H*W)
   const float* pred;
   const float* gt;
   float* dmu1;             // scratch [planes][H][W]
@@ -251,7 +251,8 @@ size_t refine_loss_scratch_bytes(int V, int H, int W) {
   return 3 * planes * N * sizeof(float) + 256 + nblk * sizeof(double) + 256;
 }
 
-void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float* loss_sum,
+void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float grad_scale,
+                        float* loss_sum,
                         float* dpred, char* scratch, cudaStream_t s) {
   LossParams p;
   {
@@ -261,7 +262,7 @@ void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W,
     for (int x = 0; x < 11; x++) p.win[x] = gf[x] / fsum;
   }
   p.planes = V * 3; p.H = H; p.W = W; p.plane_per_view = 3; p.lambda = lambda;
-  p.inv_n = 1.0f / (3.0f * (float)H * (float)W);
+  p.inv_n = grad_scale / (3.0f * (float)H * (float)W);  // only dL_dpred uses it; the loss value is finished in double
   p.pred = pred; p.gt = gt; p.dpred = dpred;
   size_t N = (size_t)H * W, planes = (size_t)V * 3;
   p.dmu1 = reinterpret_cast<float*>(scratch);

@@ -119,6 +119,11 @@ FwdRet forward_impl(const torch::Tensor& background, const torch::Tensor& means3
 using BwdRet = std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor,
                           torch::Tensor, torch::Tensor>;
 
+// Caller-provided destinations for the per-Gaussian gradients (contiguous float32 CUDA tensors of the right size).
+struct BwdDest {
+  torch::Tensor means3D, sh, opacity, scales, rotations;
+};
+
 BwdRet backward_impl(const torch::Tensor& background, const torch::Tensor& means3D, const torch::Tensor& radii,
                      const torch::Tensor& colors, const torch::Tensor& scales, const torch::Tensor& rotations,
                      float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
@@ -129,7 +134,8 @@ BwdRet backward_impl(const torch::Tensor& background, const torch::Tensor& means
                      const torch::Tensor& dL_dout_normal, const torch::Tensor& normalmap, const torch::Tensor& sh,
                      int degree, const torch::Tensor& campos, const torch::Tensor& geomBuffer, int R,
                      const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer, const torch::Tensor& alphas,
-                     bool require_coord, bool require_depth, bool debug, int V, bool batched) {
+                     bool require_coord, bool require_depth, bool debug, int V, bool batched,
+                     const BwdDest* dest = nullptr) {
   TORCH_CHECK(means3D.is_cuda(), "means3D must be a CUDA tensor (this rasterizer has no CPU path)");
   const c10::cuda::CUDAGuard guard(means3D.device());
   const int P = (int)means3D.size(0);
@@ -137,14 +143,15 @@ BwdRet backward_impl(const torch::Tensor& background, const torch::Tensor& means
   int M = 0;
   if (sh.defined() && sh.numel() != 0) M = (int)sh.size(1);
   auto fopt = means3D.options().dtype(torch::kFloat32);
-  torch::Tensor dL_dmeans3D = torch::empty({P, 3}, fopt);
+  // `dest` lets the fused refine step have the per-Gaussian gradients written in place (packed gradient record)
+  torch::Tensor dL_dmeans3D = dest ? dest->means3D : torch::empty({P, 3}, fopt);
   torch::Tensor dL_dmeans2D = batched ? torch::empty({V, P, 3}, fopt) : torch::empty({P, 3}, fopt);
   torch::Tensor dL_dcolors = torch::empty({P, 3}, fopt);
-  torch::Tensor dL_dopacity = torch::empty({P, 1}, fopt);
+  torch::Tensor dL_dopacity = dest ? dest->opacity : torch::empty({P, 1}, fopt);
   torch::Tensor dL_dcov3D = torch::empty({P, 6}, fopt);
-  torch::Tensor dL_dsh = torch::empty({P, M, 3}, fopt);
-  torch::Tensor dL_dscales = torch::zeros({P, 3}, fopt);
-  torch::Tensor dL_drotations = torch::zeros({P, 4}, fopt);
+  torch::Tensor dL_dsh = dest ? dest->sh : torch::empty({P, M, 3}, fopt);
+  torch::Tensor dL_dscales = dest ? dest->scales : torch::zeros({P, 3}, fopt);
+  torch::Tensor dL_drotations = dest ? dest->rotations : torch::zeros({P, 4}, fopt);
   if (P != 0) {
     torch::Tensor bg = contig(background), m3 = contig(means3D), col = contig(colors), sc = contig(scales),
                   rot = contig(rotations), c3 = contig(cov3D_precomp), vm = contig(viewmatrix), pm = contig(projmatrix),
@@ -310,7 +317,8 @@ void AdamStep(torch::Tensor& param, const torch::Tensor& grad, torch::Tensor& ex
         "adam_step");
 }
 
-std::tuple<torch::Tensor, torch::Tensor> RefineLoss(const torch::Tensor& pred, const torch::Tensor& gt, double lambda_l1) {
+std::tuple<torch::Tensor, torch::Tensor> RefineLoss(const torch::Tensor& pred, const torch::Tensor& gt, double lambda_l1,
+                                                    double grad_scale) {
   TORCH_CHECK(pred.is_cuda() && gt.is_cuda(), "refine_loss needs CUDA tensors (there is no CPU path)");
   TORCH_CHECK(pred.dim() == 4 && pred.size(1) == 3 && pred.sizes() == gt.sizes(), "pred/gt must be [V,3,H,W]");
   TORCH_CHECK(pred.scalar_type() == torch::kFloat32 && gt.scalar_type() == torch::kFloat32, "float32 only");
@@ -320,14 +328,146 @@ std::tuple<torch::Tensor, torch::Tensor> RefineLoss(const torch::Tensor& pred, c
   torch::Tensor dpred = torch::empty_like(p);
   torch::Tensor temp = torch::empty({0}, torch::TensorOptions().dtype(torch::kByte).device(p.device()));
   check(igs_refine_loss(p.data_ptr<float>(), g.data_ptr<float>(), (int)p.size(0), (int)p.size(2), (int)p.size(3),
-                        (float)lambda_l1, loss.data_ptr<float>(), dpred.data_ptr<float>(), tensor_alloc, &temp,
+                        (float)lambda_l1, (float)grad_scale, loss.data_ptr<float>(), dpred.data_ptr<float>(), tensor_alloc,
+                        &temp,
                         (void*)at::cuda::getCurrentCUDAStream().stream()),
         "refine_loss");
   return std::make_tuple(loss, dpred);
 }
 
+// Adam over the packed parameter record: one launch for all groups.
+void AdamStepGroups(torch::Tensor& param, const torch::Tensor& grad, torch::Tensor& exp_avg, torch::Tensor& exp_avg_sq,
+                    const std::vector<int64_t>& sizes, const std::vector<double>& lrs, double beta1, double beta2,
+                    double eps, int64_t step) {
+  TORCH_CHECK(param.is_cuda() && grad.is_cuda() && exp_avg.is_cuda() && exp_avg_sq.is_cuda(), "Adam tensors must be CUDA");
+  TORCH_CHECK(param.is_contiguous() && grad.is_contiguous() && exp_avg.is_contiguous() && exp_avg_sq.is_contiguous(),
+              "Adam tensors must be contiguous");
+  TORCH_CHECK(param.scalar_type() == torch::kFloat32 && grad.scalar_type() == torch::kFloat32, "Adam tensors must be float32");
+  TORCH_CHECK(sizes.size() == lrs.size() && sizes.size() <= 8, "at most 8 groups, one learning rate each");
+  int64_t total = 0;
+  std::vector<size_t> sz;
+  std::vector<float> lr;
+  for (size_t k = 0; k < sizes.size(); k++) { total += sizes[k]; sz.push_back((size_t)sizes[k]); lr.push_back((float)lrs[k]); }
+  TORCH_CHECK(total == param.numel() && total == grad.numel() && total == exp_avg.numel() && total == exp_avg_sq.numel(),
+              "group sizes must add up to the buffer size");
+  const c10::cuda::CUDAGuard guard(param.device());
+  check(igs_adam_step_groups(param.data_ptr<float>(), grad.data_ptr<float>(), exp_avg.data_ptr<float>(),
+                             exp_avg_sq.data_ptr<float>(), (int)sz.size(), sz.data(), lr.data(), (float)beta1,
+                             (float)beta2, (float)eps, (int)step, (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "adam_step_groups");
+}
+
+// (scales [P,3], rotations [P,4], opacities [P,1]) = activations of the raw refine parameters
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> ActivateForward(const torch::Tensor& log_scales,
+                                                                        const torch::Tensor& raw_rot,
+                                                                        const torch::Tensor& logit) {
+  TORCH_CHECK(log_scales.is_cuda(), "activations need CUDA tensors (there is no CPU path)");
+  const c10::cuda::CUDAGuard guard(log_scales.device());
+  const int P = (int)log_scales.size(0);
+  torch::Tensor ls = log_scales.contiguous(), rr = raw_rot.contiguous(), lg = logit.contiguous();
+  torch::Tensor sc = torch::empty({P, 3}, ls.options()), rot = torch::empty({P, 4}, ls.options()),
+                op = torch::empty({P, 1}, ls.options());
+  check(igs_activate_forward(P, fptr(ls, "log_scales"), fptr(rr, "raw_rot"), fptr(lg, "logit"), sc.data_ptr<float>(),
+                             rot.data_ptr<float>(), op.data_ptr<float>(),
+                             (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "activate_forward");
+  return std::make_tuple(sc, rot, op);
+}
+
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> ActivateBackward(
+    const torch::Tensor& scales, const torch::Tensor& raw_rot, const torch::Tensor& opac, const torch::Tensor& g_scales,
+    const torch::Tensor& g_rot, const torch::Tensor& g_opac) {
+  TORCH_CHECK(scales.is_cuda(), "activations need CUDA tensors (there is no CPU path)");
+  const c10::cuda::CUDAGuard guard(scales.device());
+  const int P = (int)scales.size(0);
+  torch::Tensor sc = scales.contiguous(), rr = raw_rot.contiguous(), op = opac.contiguous(), gs = g_scales.contiguous(),
+                gr = g_rot.contiguous(), go = g_opac.contiguous();
+  torch::Tensor d_ls = torch::empty({P, 3}, sc.options()), d_rr = torch::empty({P, 4}, sc.options()),
+                d_lg = torch::empty({P, 1}, sc.options());
+  check(igs_activate_backward(P, fptr(sc, "scales"), fptr(rr, "raw_rot"), fptr(op, "opac"), fptr(gs, "g_scales"),
+                              fptr(gr, "g_rot"), fptr(go, "g_opac"), d_ls.data_ptr<float>(), d_rr.data_ptr<float>(),
+                              d_lg.data_ptr<float>(), (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "activate_backward");
+  return std::make_tuple(d_ls, d_rr, d_lg);
+}
+
+// This rank's share of one refine iteration with NO autograd graph and no per-op Python:
+//   activations -> batched forward -> fused loss (dL/dcolor scaled by 1/total_views) -> backward ->
+//   activation chain rule, with every per-Gaussian gradient written in place into the packed record `grad`.
+// `flat` / `grad` are the [P*59] parameter / gradient records; offs = element offsets of
+// (xyz, rotation, shs, opacity, scaling) inside them.  Returns (loss_sum/total_views [device scalar],
+// num_rendered, radii [V,P], dL_dmeans2D [V,P,3]).
+// Mirrors infer_batch.py:279-324 for V views at once (see igs_b200/refine.py).
+std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor> RefineGrad(
+    const torch::Tensor& flat, torch::Tensor& grad, const std::vector<int64_t>& offs, int64_t P64,
+    const torch::Tensor& background, const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices,
+    const torch::Tensor& campos, double tan_fovx, double tan_fovy, double kernel_size, double scale_modifier, int H,
+    int W, int degree, const torch::Tensor& gt, int64_t total_views, double lambda_l1, bool require_coord,
+    bool require_depth, bool debug) {
+  TORCH_CHECK(flat.is_cuda() && grad.is_cuda(), "refine_grad needs CUDA tensors (there is no CPU path)");
+  TORCH_CHECK(flat.is_contiguous() && grad.is_contiguous() && flat.numel() == grad.numel(), "flat/grad must be contiguous and equal-sized");
+  TORCH_CHECK(flat.scalar_type() == torch::kFloat32 && grad.scalar_type() == torch::kFloat32, "float32 only");
+  TORCH_CHECK(offs.size() == 5, "offs = (xyz, rotation, shs, opacity, scaling)");
+  TORCH_CHECK(viewmatrices.dim() == 3, "viewmatrices must be [V,4,4]");
+  const c10::cuda::CUDAGuard guard(flat.device());
+  const int P = (int)P64;
+  const int V = (int)viewmatrices.size(0);
+  TORCH_CHECK(gt.dim() == 4 && gt.size(0) == V && gt.size(1) == 3 && gt.size(2) == H && gt.size(3) == W, "gt must be [V,3,H,W]");
+  TORCH_CHECK(total_views >= 1, "total_views must be >= 1");
+  auto slice = [&](const torch::Tensor& buf, int k, int64_t per, std::vector<int64_t> shape) {
+    return buf.narrow(0, offs[k], (int64_t)P * per).view(shape);
+  };
+  torch::Tensor xyz = slice(flat, 0, 3, {P, 3}), raw_rot = slice(flat, 1, 4, {P, 4}), shs = slice(flat, 2, 48, {P, 16, 3}),
+                logit = slice(flat, 3, 1, {P, 1}), log_sc = slice(flat, 4, 3, {P, 3});
+  cudaStream_t stream = at::cuda::getCurrentCUDAStream();
+  // activated parameters and their gradients: one 16P-float slab (rotations first: float4-aligned)
+  torch::Tensor slab = torch::empty({(int64_t)P * 16}, flat.options());
+  torch::Tensor rot = slab.narrow(0, 0, (int64_t)P * 4).view({P, 4}), g_rot = slab.narrow(0, (int64_t)P * 4, (int64_t)P * 4).view({P, 4}),
+                sc = slab.narrow(0, (int64_t)P * 8, (int64_t)P * 3).view({P, 3}), g_sc = slab.narrow(0, (int64_t)P * 11, (int64_t)P * 3).view({P, 3}),
+                op = slab.narrow(0, (int64_t)P * 14, P).view({P, 1}), g_op = slab.narrow(0, (int64_t)P * 15, P).view({P, 1});
+  check(igs_activate_forward(P, log_sc.data_ptr<float>(), raw_rot.data_ptr<float>(), logit.data_ptr<float>(),
+                             sc.data_ptr<float>(), rot.data_ptr<float>(), op.data_ptr<float>(), (void*)stream),
+        "activate_forward");
+  torch::Tensor none;
+  FwdRet f = forward_impl(background, xyz, none, op, sc, rot, (float)scale_modifier, none, viewmatrices, projmatrices,
+                          (float)tan_fovx, (float)tan_fovy, (float)kernel_size, H, W, shs, degree, campos, false,
+                          require_coord, require_depth, debug, V, true);
+  const int rendered = std::get<0>(f);
+  const torch::Tensor& color = std::get<1>(f);
+  torch::Tensor loss = torch::zeros({}, flat.options());
+  torch::Tensor dcolor = torch::empty_like(color);
+  torch::Tensor temp = torch::empty({0}, torch::TensorOptions().dtype(torch::kByte).device(flat.device()));
+  torch::Tensor gtc = gt.contiguous();
+  TORCH_CHECK(gtc.is_cuda() && gtc.scalar_type() == torch::kFloat32, "gt must be a float32 CUDA tensor");
+  const float gscale = 1.0f / (float)total_views;
+  check(igs_refine_loss(color.data_ptr<float>(), gtc.data_ptr<float>(), V, H, W, (float)lambda_l1, gscale,
+                        loss.data_ptr<float>(), dcolor.data_ptr<float>(), tensor_alloc, &temp, (void*)stream),
+        "refine_loss");
+  BwdDest dest;
+  dest.means3D = slice(grad, 0, 3, {P, 3});
+  dest.sh = slice(grad, 2, 48, {P, 16, 3});
+  dest.opacity = g_op; dest.scales = g_sc; dest.rotations = g_rot;
+  BwdRet b = backward_impl(background, xyz, std::get<8>(f), none, sc, rot, (float)scale_modifier, none, viewmatrices,
+                           projmatrices, (float)tan_fovx, (float)tan_fovy, (float)kernel_size, dcolor, none, none, none,
+                           none, none, none, std::get<5>(f), shs, degree, campos, std::get<9>(f), rendered,
+                           std::get<10>(f), std::get<11>(f), std::get<4>(f), require_coord, require_depth, debug, V, true,
+                           &dest);
+  check(igs_activate_backward(P, sc.data_ptr<float>(), raw_rot.data_ptr<float>(), op.data_ptr<float>(),
+                              g_sc.data_ptr<float>(), g_rot.data_ptr<float>(), g_op.data_ptr<float>(),
+                              slice(grad, 4, 3, {P, 3}).data_ptr<float>(), slice(grad, 1, 4, {P, 4}).data_ptr<float>(),
+                              slice(grad, 3, 1, {P, 1}).data_ptr<float>(), (void*)stream),
+        "activate_backward");
+  loss.mul_(gscale);
+  return std::make_tuple(loss, (int64_t)rendered, std::get<8>(f), std::get<0>(b));
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
-  m.def("refine_loss", &RefineLoss);
+  m.def("refine_loss", &RefineLoss, pybind11::arg("pred"), pybind11::arg("gt"), pybind11::arg("lambda_l1"),
+        pybind11::arg("grad_scale") = 1.0);
+  m.def("refine_grad", &RefineGrad);
+  m.def("activate_forward", &ActivateForward);
+  m.def("activate_backward", &ActivateBackward);
+  m.def("adam_step_groups", &AdamStepGroups);
   m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
   m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
   m.def("mark_visible", &markVisible);

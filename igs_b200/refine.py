@@ -68,12 +68,15 @@ class RefineState:
 
     def adam_step(self) -> None:
         """torch.optim.Adam(lr per group, betas=(0.9,0.999), eps=1e-15) — gaussian_model.py:348 — as one
-        fused kernel launch per parameter group (igs_adam_step)."""
+        fused kernel launch over all parameter groups (igs_adam_step_groups)."""
         self.step += 1
-        for name, _ in GROUPS:
-            a, b, _k = self.slices[name]
-            _C.adam_step(self.flat[a:b], self.grad[a:b], self.exp_avg[a:b], self.exp_avg_sq[a:b],
-                         float(self.lrs[name]), 0.9, 0.999, 1e-15, self.step)
+        _C.adam_step_groups(self.flat, self.grad, self.exp_avg, self.exp_avg_sq,
+                            [self.P * k for _, k in GROUPS], [float(self.lrs[n]) for n, _ in GROUPS],
+                            0.9, 0.999, 1e-15, self.step)
+
+    def offsets(self):
+        """Element offsets of (xyz, rotation, shs, opacity, scaling) in the packed record (refine_grad's `offs`)."""
+        return [self.slices[n][0] for n in ("xyz", "rotation", "shs", "opacity", "scaling")]
 
 
 # ------------------------------------------------------------------------------------------------
@@ -118,7 +121,7 @@ class _FusedLoss(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, pred, gt, lambda_l1):
-        loss_sum, dpred = _C.refine_loss(pred, gt, float(lambda_l1))
+        loss_sum, dpred = _C.refine_loss(pred, gt, float(lambda_l1), 1.0)
         ctx.save_for_backward(dpred)
         return loss_sum
 
@@ -154,18 +157,35 @@ def forward_views(state: RefineState, settings: MultiViewSettings):
 
 
 def refine_iteration(state: RefineState, settings: MultiViewSettings, gt: torch.Tensor, total_views: int,
-                     group=None, lambda_l1: float = 0.8, loss_impl: str = "fused", do_step: bool = True) -> IterationResult:
+                     group=None, lambda_l1: float = 0.8, loss_impl: str = "fused", do_step: bool = True,
+                     impl: str = "native") -> IterationResult:
     """One Adam step on `total_views` views, of which this rank renders `settings.viewmatrices.shape[0]`.
 
     loss = (1/total_views) * sum_v [lambda*L1_v + (1-lambda)*(1-SSIM_v)]; gradients are summed over ranks.
+
+    impl="native" (default with the fused loss) runs activations -> forward -> loss -> backward -> activation chain
+    rule in ONE native call (`_C.refine_grad`) that writes the packed gradient record in place: no autograd graph,
+    no per-op Python.  impl="autograd" is the same computation through torch autograd over `rasterize_views`
+    (what a reference user's loop looks like); the two agree to fp32 rounding (tests/test_refine_gpu.py).
     """
+    Vl = int(settings.viewmatrices.shape[0]) if settings is not None else 0
+    if impl == "native" and loss_impl == "fused" and Vl > 0:
+        s = settings
+        loss, R, radii, g2d = _C.refine_grad(
+            state.flat, state.grad, state.offsets(), state.P, s.bg, s.viewmatrices, s.projmatrices, s.campos,
+            float(s.tanfovx), float(s.tanfovy), float(s.kernel_size), float(s.scale_modifier), int(s.image_height),
+            int(s.image_width), int(s.sh_degree), gt, int(total_views), float(lambda_l1), bool(s.require_coord),
+            bool(s.require_depth), bool(s.debug))
+        loss = reduce_gradients(state.grad, loss, group)
+        if do_step:
+            state.adam_step()
+        return IterationResult(loss, int(R), radii, g2d)
     names = [n for n, _ in GROUPS]
     leaves = []
     for n in names:
         p = state.param(n).detach().requires_grad_(True)
         leaves.append(p)
     lv = dict(zip(names, leaves))
-    Vl = int(settings.viewmatrices.shape[0]) if settings is not None else 0
     if Vl > 0:
         scales = torch.exp(lv["scaling"])
         rot = F.normalize(lv["rotation"])
@@ -202,7 +222,7 @@ def reduce_gradients(flat_grad: torch.Tensor, loss: torch.Tensor, group=None) ->
         return loss
     torch.distributed.all_reduce(flat_grad, group=group)
     loss = loss.clone()
-    torch.distributed.all_reduce(loss, group=group)
+    torch.distributed.all_reduce(loss, group=group)  # 4 bytes; kept separate so `flat_grad` stays the plain record
     return loss
 
 

@@ -17,8 +17,10 @@
  *   igs_decode_binning      <- (test/inspection only) exposes what the reference keeps in BinningState /
  *                              ImageState (DGR/cuda_rasterizer/rasterizer_impl.h:64-86): sorted 64-bit keys,
  *                              point_list, tile ranges, n_contrib.
- *   igs_adam_step           <- torch.optim.Adam(eps=1e-15) over the refine parameters
+ *   igs_adam_step(_groups)  <- torch.optim.Adam(eps=1e-15) over the refine parameters
  *                              (igs/models/gaussian_model.py:348; infer_batch.py:323)
+ *   igs_refine_loss         <- 0.8*L1 + 0.2*(1-SSIM) (infer_batch.py:301-305, igs/utils/loss_utils.py:16-62)
+ *   igs_activate_forward/backward <- exp / normalize / sigmoid activations (igs/models/gaussian_model.py:89-127)
  *
  * Conventions
  *   - All pointers are DEVICE pointers unless stated otherwise; float = IEEE fp32; layouts are the
@@ -53,7 +55,7 @@
 extern "C" {
 #endif
 
-#define IGS_RASTER_ABI_VERSION 1
+#define IGS_RASTER_ABI_VERSION 2
 
 typedef enum igs_status {
   IGS_OK = 0,
@@ -195,12 +197,35 @@ int igs_decode_binning(int P, int V, int R, int width, int height,
 int igs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_avg_sq,
                   size_t n, float lr, float beta1, float beta2, float eps, int step, void* stream);
 
+/* Adam over `ngroups` (<= 8) CONTIGUOUS parameter groups of one flat buffer in ONE launch: group k covers
+ * sizes[k] floats after the previous group and uses learning rate lrs[k] (HOST arrays).  Same arithmetic as
+ * igs_adam_step; replaces the per-group loop of torch.optim.Adam over GaussianModel.training_setup's groups
+ * (igs/models/gaussian_model.py:265-348). */
+int igs_adam_step_groups(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int ngroups,
+                         const size_t* sizes, const float* lrs, float beta1, float beta2, float eps, int step,
+                         void* stream);
+
 /* Fused refine loss over V images [V][3][H][W] (replaces infer_batch.py:301-305 with igs/utils/loss_utils.py:16-62):
  *   *loss_sum = sum_v [ lambda * mean|pred_v - gt_v| + (1 - lambda) * (1 - mean SSIM(pred_v, gt_v)) ]
- *   dL_dpred  = d(*loss_sum) / d(pred)            (11x11 Gaussian window, sigma 1.5, zero padding)
- * loss_sum is a DEVICE float; temp_alloc provides 36*V*H*W bytes (+ a few KB) of scratch. */
+ *   dL_dpred  = grad_scale * d(*loss_sum) / d(pred)     (11x11 Gaussian window, sigma 1.5, zero padding)
+ * grad_scale is the upstream gradient of loss_sum (1/total_views when the step's loss is the mean over views);
+ * loss_sum itself is NOT scaled.  loss_sum is a DEVICE float; temp_alloc provides 36*V*H*W bytes (+ a few KB). */
 int igs_refine_loss(const float* pred, const float* gt, int V, int height, int width, float lambda_l1,
-                    float* loss_sum, float* dL_dpred, igs_alloc_fn temp_alloc, void* temp_user, void* stream);
+                    float grad_scale, float* loss_sum, float* dL_dpred, igs_alloc_fn temp_alloc, void* temp_user,
+                    void* stream);
+
+/* Parameter activations of the refine loop and their chain rule (igs/models/gaussian_model.py:89-127, i.e.
+ * RaDe-GS scene/gaussian_model.py setup_functions: scaling = exp, rotation = F.normalize (eps 1e-12),
+ * opacity = sigmoid), one launch each instead of one torch kernel + autograd node per activation.
+ *   forward : scales[P][3] = exp(log_scales), rotations[P][4] = raw_rot / max(|raw_rot|, 1e-12),
+ *             opacities[P] = sigmoid(opacity_logit)
+ *   backward: dL_dlog_scales = dL_dscales * scales;  dL_draw_rot = (dL_drot - y (y . dL_drot)) / |raw_rot|;
+ *             dL_dlogit = dL_dopac * o (1 - o).  Output pointers may alias the matching dL_d* input (in place). */
+int igs_activate_forward(int P, const float* log_scales, const float* raw_rot, const float* opacity_logit,
+                         float* scales, float* rotations, float* opacities, void* stream);
+int igs_activate_backward(int P, const float* scales, const float* raw_rot, const float* opacities,
+                          const float* dL_dscales, const float* dL_drot, const float* dL_dopac,
+                          float* dL_dlog_scales, float* dL_draw_rot, float* dL_dlogit, void* stream);
 
 const char* igs_last_error(void);
 int igs_abi_version(void);

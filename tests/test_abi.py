@@ -24,7 +24,8 @@ def lib(native):
 def test_header_declares_the_expected_entry_points():
     fns = declared_functions()
     for must in ("igs_rasterize_forward", "igs_rasterize_backward", "igs_mark_visible", "igs_decode_binning",
-                 "igs_adam_step", "igs_last_error", "igs_abi_version", "igs_kernel_launches"):
+                 "igs_adam_step", "igs_adam_step_groups", "igs_refine_loss", "igs_activate_forward",
+                 "igs_activate_backward", "igs_last_error", "igs_abi_version", "igs_kernel_launches"):
         assert must in fns
 
 
@@ -34,7 +35,7 @@ def test_every_declared_symbol_is_exported(lib):
 
 
 def test_abi_version(lib):
-    assert lib.igs_abi_version() == 1
+    assert lib.igs_abi_version() == 2
 
 
 def test_null_arguments_are_rejected_without_touching_the_gpu(lib):
@@ -49,7 +50,8 @@ def test_null_arguments_are_rejected_without_touching_the_gpu(lib):
 def test_python_extension_exports_reference_entry_points(native):
     for name in ("rasterize_gaussians", "rasterize_gaussians_backward", "mark_visible"):  # DGR/ext.cpp:15-19
         assert hasattr(native, name)
-    for name in ("rasterize_views", "rasterize_views_backward", "adam_step", "decode_buffers", "kernel_launches"):
+    for name in ("rasterize_views", "rasterize_views_backward", "adam_step", "adam_step_groups", "refine_loss",
+                 "refine_grad", "activate_forward", "activate_backward", "decode_buffers", "kernel_launches"):
         assert hasattr(native, name)
 
 
@@ -65,6 +67,12 @@ def test_no_cpu_fallback(native):
                                    torch.zeros(3), False, True, True, False)
     with pytest.raises(RuntimeError):
         native.mark_visible(m, torch.eye(4), torch.eye(4))
+    with pytest.raises(RuntimeError, match="CUDA"):
+        native.refine_grad(torch.zeros(4 * 59), torch.zeros(4 * 59), [0, 12, 28, 220, 224], 4, torch.zeros(3),
+                           torch.eye(4)[None], torch.eye(4)[None], torch.zeros(1, 3), 1.0, 1.0, 0.0, 1.0, 16, 16, 3,
+                           torch.zeros(1, 3, 16, 16), 1, 0.8, True, True, False)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        native.activate_forward(torch.zeros(4, 3), torch.ones(4, 4), torch.zeros(4, 1))
 
 
 def test_product_never_imports_the_oracle():

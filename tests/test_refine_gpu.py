@@ -106,3 +106,83 @@ def test_sharded_gradients_equal_single_batch(cuda_dev, native):
         loss += float(r.loss)
     assert abs(loss - float(r_all.loss)) <= 1e-5 * abs(loss)
     assert float((total - g_all).abs().max()) <= 1e-4 * float(g_all.abs().max())
+
+
+def test_native_step_matches_autograd_step(cuda_dev, native):
+    """_C.refine_grad (no autograd graph, gradients written in place into the packed record) against the same
+    iteration through torch autograd over rasterize_views: bit-identical when both use the activation kernels,
+    and within the gradient parity bar when autograd uses torch's exp / normalize / sigmoid (their one-ulp
+    differences in the activated parameters move the ill-conditioned position gradients by a few 1e-4)."""
+    import tolerances
+    from igs_b200 import refine
+    from igs_b200.multiview import rasterize_views
+    P, V, W, H = 20001, 3, 176, 120   # odd P: the record's slices are not 16-byte aligned
+    state, st = _state_and_settings(cuda_dev, P, V, W, H)
+    gen = torch.Generator().manual_seed(11)
+    gt = torch.rand(V, 3, H, W, generator=gen).to(cuda_dev)
+    # total_views = 8: the 1/total_views scaling of dL/dcolor is exact in every path
+    ra = refine.refine_iteration(state, st, gt, 8, do_step=False, impl="autograd")
+    g_auto = state.grad.clone()
+    state.grad.fill_(float("nan"))   # every element must be overwritten
+    rn = refine.refine_iteration(state, st, gt, 8, do_step=False, impl="native")
+    g_nat = state.grad.clone()
+    assert rn.num_rendered == ra.num_rendered and torch.equal(rn.radii, ra.radii)
+    assert abs(float(rn.loss) - float(ra.loss)) <= 1e-6 * abs(float(ra.loss))
+    assert bool(torch.isfinite(g_nat).all())
+    for name, _ in refine.GROUPS:
+        a, b, _k = state.slices[name]
+        scale = float(g_auto[a:b].abs().max())
+        assert float((g_nat[a:b] - g_auto[a:b]).abs().max()) <= tolerances.GRAD_RTOL * scale, name
+    # same activated inputs -> same kernels -> identical bits
+    sc, rot, op = native.activate_forward(state.param("scaling"), state.param("rotation"), state.param("opacity"))
+    leaves = [t.detach().clone().requires_grad_(True) for t in (state.param("xyz"), state.param("shs"), op, sc, rot)]
+    color = rasterize_views(*leaves, st)[0]
+    loss = refine.refine_loss_sum(color, gt, 0.8, "fused") / 8.0
+    g_xyz, g_sh, g_op, g_sc, g_rot = torch.autograd.grad(loss, leaves)
+    d_ls, d_rr, d_lg = native.activate_backward(sc, state.param("rotation"), op, g_sc, g_rot, g_op)
+    for name, ref in (("xyz", g_xyz), ("shs", g_sh), ("scaling", d_ls), ("rotation", d_rr), ("opacity", d_lg)):
+        a, b, _k = state.slices[name]
+        assert torch.equal(g_nat[a:b], ref.reshape(-1)), name
+    assert torch.equal(rn.grad_means2D, color.grad_fn.grad_means2D)
+    assert float(rn.loss) == float(loss)
+
+
+def test_activation_kernels_match_torch(cuda_dev, native):
+    import torch.nn.functional as F
+    gen = torch.Generator().manual_seed(12)
+    P = 4099
+    ls = (torch.randn(P, 3, generator=gen) - 2).to(cuda_dev).requires_grad_(True)
+    rr = torch.randn(P, 4, generator=gen).to(cuda_dev)
+    rr[:5] *= 1e-3
+    rr.requires_grad_(True)
+    lg = (3 * torch.randn(P, 1, generator=gen)).to(cuda_dev).requires_grad_(True)
+    sc, rot, op = native.activate_forward(ls.detach(), rr.detach(), lg.detach())
+    tsc, trot, top = torch.exp(ls), F.normalize(rr), torch.sigmoid(lg)
+    assert float((sc - tsc).abs().max()) <= 2e-7 * float(tsc.abs().max())
+    assert float((rot - trot).abs().max()) <= 3e-7
+    assert float((op - top).abs().max()) <= 2e-7
+    gs, gr, go = (torch.randn(P, 3, generator=gen).to(cuda_dev), torch.randn(P, 4, generator=gen).to(cuda_dev),
+                  torch.randn(P, 1, generator=gen).to(cuda_dev))
+    ((tsc * gs).sum() + (trot * gr).sum() + (top * go).sum()).backward()
+    d_ls, d_rr, d_lg = native.activate_backward(sc, rr.detach(), op, gs, gr, go)
+    assert float((d_ls - ls.grad).abs().max()) <= 1e-6 * float(ls.grad.abs().max())
+    assert float(((d_rr - rr.grad).abs() / (rr.grad.abs() + 1e-3 * rr.grad.abs().max())).max()) <= 1e-4
+    assert float((d_lg - lg.grad).abs().max()) <= 1e-6 * float(lg.grad.abs().max())
+
+
+def test_grouped_adam_matches_per_group_adam(cuda_dev, native):
+    gen = torch.Generator().manual_seed(13)
+    sizes = [3001, 4000, 48017, 1000, 3003]
+    lrs = [0.0016, 0.01, 0.0025, 0.05, 0.005]
+    n = sum(sizes)
+    p0 = torch.randn(n, generator=gen).to(cuda_dev)
+    a, ma, va = p0.clone(), torch.zeros(n, device=cuda_dev), torch.zeros(n, device=cuda_dev)
+    b, mb, vb = p0.clone(), torch.zeros(n, device=cuda_dev), torch.zeros(n, device=cuda_dev)
+    for step in range(1, 4):
+        g = torch.randn(n, generator=gen).to(cuda_dev)
+        native.adam_step_groups(a, g, ma, va, sizes, lrs, 0.9, 0.999, 1e-15, step)
+        off = 0
+        for sz, lr in zip(sizes, lrs):
+            native.adam_step(b[off:off + sz], g[off:off + sz], mb[off:off + sz], vb[off:off + sz], lr, 0.9, 0.999, 1e-15, step)
+            off += sz
+        assert torch.equal(a, b) and torch.equal(ma, mb) and torch.equal(va, vb)
