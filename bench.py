@@ -71,6 +71,8 @@ class ClockSampler:
         self.rows = []
         self.proc = None
         self.thread = None
+        self.t0 = None
+        self.t1 = None
 
     def start(self):
         try:
@@ -85,7 +87,15 @@ class ClockSampler:
 
     def _read(self):
         for line in self.proc.stdout:
-            self.rows.append(line.strip())
+            self.rows.append((time.monotonic(), line.strip()))
+
+    # The sampler is started BEFORE the warm-up (spawning nvidia-smi stalls the launching thread for tens of
+    # milliseconds); only samples taken between begin() and end() — the timed region — are reported.
+    def begin(self):
+        self.t0 = time.monotonic()
+
+    def end(self):
+        self.t1 = time.monotonic()
 
     def stop(self) -> dict:
         if self.proc is None:
@@ -98,7 +108,10 @@ class ClockSampler:
             self.proc.kill()
         sm, mx, reasons, power = [], [], set(), []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for r in self.rows:
+        rows = [r for t, r in self.rows if self.t0 is None or self.t1 is None or (self.t0 <= t <= self.t1 + 0.1)]
+        if not rows:
+            rows = [r for _t, r in self.rows]
+        for r in rows:
             f = [x.strip() for x in r.split(",")]
             if len(f) < 9:
                 continue
@@ -323,16 +336,18 @@ def main():
         return float(ms.item()) / steps, last
 
     # ---- (1) device-resident timing with stage timers + clocks ----
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
     for _ in range(max(args.warmup, 3)):
         step_resident()
     barrier()
     _C.stage_timing_enable(True)
     _C.stage_timing_read(True)
     launches0 = _C.kernel_launches()
-    sampler = ClockSampler(local_rank)
-    if rank == 0:
-        sampler.start()
+    sampler.begin()
     ms_step, last = timed(step_resident, args.steps, 0)
+    sampler.end()
     clocks = sampler.stop() if rank == 0 else None
     launches = _C.kernel_launches() - launches0
     stages = _C.stage_timing_read(True)

@@ -130,9 +130,11 @@ radix_hist_kernel(const K* __restrict__ keys, size_t n, int shift, uint32_t mask
 }
 
 // Each warp ranks a contiguous chunk of 512 keys in 16 rounds of 32 consecutive keys, so that the
-// rank order equals the index order (stability).
+// rank order equals the index order (stability).  The kernel is latency bound (a serial chain of 16 match/rank
+// rounds per warp), so the per-thread state is kept small — digits are recomputed from the keys and the 16 ranks
+// (< 512) are packed two per register — to hold 4 CTAs per SM.
 template <typename K, int BITS>
-__global__ void __launch_bounds__(IGS_SORT_THREADS)
+__global__ void __launch_bounds__(IGS_SORT_THREADS, sizeof(K) == 4 ? 4 : 3)
 radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, K* __restrict__ keys_out,
                      uint32_t* __restrict__ vals_out, size_t n, int shift, uint32_t mask,
                      const uint32_t* __restrict__ hist_scanned, unsigned nblocks) {
@@ -144,29 +146,32 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
   const int w = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
   for (int i = threadIdx.x; i < WARPS * (NB + 1); i += IGS_SORT_THREADS) (&whist[0][0])[i] = 0;
-  __syncthreads();
 
   const size_t wbase = (size_t)blockIdx.x * IGS_SORT_TILE + (size_t)w * CHUNK;
   K key[ROUNDS];
-  uint32_t rnk[ROUNDS];
-  uint32_t dig[ROUNDS];
+  uint32_t rnk2[ROUNDS / 2];
+#pragma unroll
+  for (int r = 0; r < ROUNDS; r++) {  // all loads first: 16 independent requests in flight
+    const size_t i = wbase + (size_t)r * 32 + lane;
+    key[r] = i < n ? keys_in[i] : K(0);
+  }
+  __syncthreads();
+  uint32_t* const myhist = whist[w];
+  const uint32_t lt_mask = (1u << lane) - 1u;
 #pragma unroll
   for (int r = 0; r < ROUNDS; r++) {
-    size_t i = wbase + (size_t)r * 32 + lane;
-    bool valid = i < n;
-    key[r] = valid ? keys_in[i] : K(0);
-    uint32_t d = valid ? digit_of<K>(key[r], shift, mask) : (uint32_t)NB;
-    dig[r] = d;
-    uint32_t peers = __match_any_sync(0xffffffffu, d);
-    uint32_t lt = peers & ((1u << lane) - 1u);
-    int leader = __ffs(peers) - 1;
+    const bool valid = wbase + (size_t)r * 32 + lane < n;
+    const uint32_t d = valid ? digit_of<K>(key[r], shift, mask) : (uint32_t)NB;
+    const uint32_t peers = __match_any_sync(0xffffffffu, d);
+    const int leader = __ffs(peers) - 1;
     uint32_t old = 0;
     if ((int)lane == leader) {
-      old = whist[w][d];
-      whist[w][d] = old + __popc(peers);
+      old = myhist[d];
+      myhist[d] = old + __popc(peers);
     }
     old = __shfl_sync(0xffffffffu, old, leader);
-    rnk[r] = old + __popc(lt);
+    const uint32_t rk = old + __popc(peers & lt_mask);
+    if (r & 1) rnk2[r >> 1] |= rk << 16; else rnk2[r >> 1] = rk;
     __syncwarp();
   }
   __syncthreads();
@@ -183,9 +188,10 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
   __syncthreads();
 #pragma unroll
   for (int r = 0; r < ROUNDS; r++) {
-    size_t i = wbase + (size_t)r * 32 + lane;
+    const size_t i = wbase + (size_t)r * 32 + lane;
     if (i < n) {
-      uint32_t pos = whist[w][dig[r]] + rnk[r];
+      const uint32_t rk = (r & 1) ? (rnk2[r >> 1] >> 16) : (rnk2[r >> 1] & 0xffffu);
+      const uint32_t pos = myhist[digit_of<K>(key[r], shift, mask)] + rk;
       keys_out[pos] = key[r];
       vals_out[pos] = vals_in[i];
     }

@@ -165,8 +165,11 @@ project_kernel(ProjectParams p, const Camera* __restrict__ cams, const float* __
                float* __restrict__ depth_out, int* __restrict__ radii_geom, int* __restrict__ radii_out,
                uint32_t* __restrict__ tiles_out, uint8_t* __restrict__ clamped_out,
                uint64_t* __restrict__ skey, uint32_t* __restrict__ sval) {
-  int g = blockIdx.x * blockDim.x + threadIdx.x;
-  int v = blockIdx.y;
+  // View index fastest in the launch order: the V CTAs that project one chunk of 256 Gaussians run together, so the
+  // per-Gaussian inputs (192 B of SH coefficients, covariance, eigen-frame) come from DRAM once and from L2 V-1 times.
+  int chunk, v;
+  if (gridDim.y == 1) { v = blockIdx.x % p.V; chunk = blockIdx.x / p.V; } else { chunk = blockIdx.x; v = blockIdx.y; }
+  int g = chunk * blockDim.x + threadIdx.x;
   if (g >= p.P) return;
   size_t gid = (size_t)v * p.P + g;
   const Camera& cam = cams[v];
@@ -354,7 +357,9 @@ void launch_gauss_setup(int P, const float* scales, float mod, const float* rota
 
 void launch_project(const ProjectParams& p, const GeomBuf& g, int* radii_out, cudaStream_t s) {
   if (p.P <= 0) return;
-  dim3 grid((p.P + 255) / 256, p.V);
+  const unsigned chunks = (unsigned)((p.P + 255) / 256);
+  dim3 grid(chunks, p.V);
+  if ((size_t)chunks * p.V < 0x7fffffffu) grid = dim3(chunks * p.V, 1);  // view-fastest linear order
   count_launch();
   project_kernel<<<grid, 256, 0, s>>>(p, g.cams, g.cov3D, g.eig, g.head, g.tail, g.depth, g.radii, radii_out,
                                       g.tiles, g.clamped, g.skey[0], g.sval[0]);

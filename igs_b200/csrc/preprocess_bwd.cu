@@ -51,7 +51,19 @@ gather_bwd_kernel(GatherBwdParams p) {
     const uint32_t n = p.inst_off[pos + 1] - off;
     if (p.ns == 16) {
       const float4* r = reinterpret_cast<const float4*>(p.grec + (size_t)off * 16);
-      for (uint32_t k = 0; k < n; k++) {
+      uint32_t k = 0;
+      for (; k + 4 <= n; k += 4) {  // 12 independent 16-byte loads in flight per thread (the kernel is latency bound)
+        float4 a[4], b[4], c[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) { a[u] = r[(k + u) * 4 + 0]; b[u] = r[(k + u) * 4 + 1]; c[u] = r[(k + u) * 4 + 2]; }
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+          s[0] += a[u].x; s[1] += a[u].y; s[2] += a[u].z; s[3] += a[u].w;
+          s[4] += b[u].x; s[5] += b[u].y; s[6] += b[u].z; s[7] += b[u].w;
+          s[8] += c[u].x; s[9] += c[u].y;
+        }
+      }
+      for (; k < n; k++) {
         float4 a = r[k * 4 + 0], b = r[k * 4 + 1], c = r[k * 4 + 2];
         s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
         s[4] += b.x; s[5] += b.y; s[6] += b.z; s[7] += b.w;
