@@ -61,8 +61,9 @@ blend_bwd_kernel(BlendBwdParams p) {
   constexpr int BATCH = bwd_batch(GEOGRAD, MINB);
   constexpr bool GEO = GEOGRAD && (COORD || DEPTH || NORMAL);
   // survivors: [0,B) head.a {x, y, conic.x, conic.y}; [B,2B) head.b {conic.z, opacity, r, g};
-  // [2B,3B) {blue, list position (bits), tau, batch slot (bits)}
+  // [2B,3B) {blue, 1.0f, list position (bits), batch slot (bits)}  ((blue, 1) is an fp32x2 operand of the recurrences)
   __shared__ float4 s_rec[BATCH * 3];
+  __shared__ float s_tau[BATCH];
   __shared__ float4 s_t[GEO ? BATCH * 4 : 1];
   __shared__ uint32_t s_gid[BATCH];
   __shared__ uint32_t s_e[BATCH];
@@ -189,9 +190,13 @@ blend_bwd_kernel(BlendBwdParams p) {
     }
   }
   const float bg_dot_dpixel = p.bg[0] * dLp0 + p.bg[1] * dLp1 + p.bg[2] * dLp2;
+  const f32x2 grad01 = pack2(dLp0, dLp1), grad2a = pack2(dLp2, dL_dalpha);
+  const f32x2 pix2 = pack2(pixfx, pixfy), half2 = pack2(p.half_w, p.half_h);
 
-  float last_alpha = 0, accum_alpha_rec = 0;
-  float ar0 = 0, ar1 = 0, ar2 = 0, lc0 = 0, lc1 = 0, lc2 = 0;      // colour recurrence
+  float last_alpha = 0;
+  // colour + alpha recurrences as two fp32x2 pairs: acc01 = (accum_rec r, g), acc2a = (accum_rec b, accum_alpha_rec);
+  // last01 = (last colour r, g), last2o = (last colour b, 1);  grad01 = (dL/dpixel r, g), grad2a = (dL/dpixel b, dL/dalpha)
+  f32x2 acc01 = pack2(0.0f, 0.0f), acc2a = pack2(0.0f, 0.0f), last01 = pack2(0.0f, 0.0f), last2o = pack2(0.0f, 1.0f);
   float cr0 = 0, cr1 = 0, cr2 = 0, lco0 = 0, lco1 = 0, lco2 = 0;  // coord recurrence
   float tr = 0, lt = 0;                                            // depth recurrence
   float nr0 = 0, nr1 = 0, nr2 = 0, ln0 = 0, ln1 = 0, ln2 = 0;      // normal recurrence
@@ -227,7 +232,8 @@ blend_bwd_kernel(BlendBwdParams p) {
       uint32_t k = woff + __popc(bal & ((1u << lane) - 1u));
       s_rec[k] = ha;
       s_rec[BATCH + k] = hb;
-      s_rec[2 * BATCH + k] = make_float4(p.tail[gid].a.x, __uint_as_float(j - range.x + 1), tau, __uint_as_float(threadIdx.x));
+      s_rec[2 * BATCH + k] = make_float4(p.tail[gid].a.x, 1.0f, __uint_as_float(j - range.x + 1), __uint_as_float(threadIdx.x));
+      s_tau[k] = tau;
       s_gid[k] = gid;
     }
     __syncthreads();
@@ -247,7 +253,7 @@ blend_bwd_kernel(BlendBwdParams p) {
         const float4 a = lds128<0>(ak);
         const float4 b = lds128<BATCH * 16>(ak);
         const float4 c = lds128<BATCH * 32>(ak);
-        hit = (__float_as_uint(c.y) <= wlast) && block_can_contribute(a.x, a.y, a.z, a.w, b.x, c.z, bx0, by0, bx1, by1);
+        hit = (__float_as_uint(c.z) <= wlast) && block_can_contribute(a.x, a.y, a.z, a.w, b.x, s_tau[k], bx0, by0, bx1, by1);
       }
       uint32_t m = __ballot_sync(0xffffffffu, hit);
       while (m) {
@@ -256,9 +262,11 @@ blend_bwd_kernel(BlendBwdParams p) {
         const uint32_t ak = rec_base + kk * 16;
         const float4 a = lds128<0>(ak);
         const float4 bq = lds128<BATCH * 16>(ak);
-        const float4 cq = lds128<BATCH * 32>(ak);  // {blue, position, tau, slot}
-        const uint32_t pos = __float_as_uint(cq.y);
-        const float dx = fsub(a.x, pixfx), dy = fsub(a.y, pixfy);
+        const float4 cq = lds128<BATCH * 32>(ak);  // {blue, 1, position, slot}
+        const uint32_t pos = __float_as_uint(cq.z);
+        const f32x2 d2 = sub2(pack2(a.x, a.y), pix2);  // (dx, dy), each rounded like fsub()
+        float dx, dy;
+        unpack2(d2, dx, dy);
         const float power = splat_power(dx, dy, a.z, a.w, bq.x);
         const float G = expf(power);
         const float alpha = fminf(0.99f, fmul(bq.y, G));
@@ -274,13 +282,17 @@ blend_bwd_kernel(BlendBwdParams p) {
           asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp) : "f"(1.0f - alpha));  // 1 - alpha is in [0.01, 1]
           T = T * rcp;
           const float aT = alpha * T;
-          float dL_dopa = 0.0f;
-          const float blue = cq.x;
-          // colour
-          ar0 = last_alpha * lc0 + (1.0f - last_alpha) * ar0; lc0 = bq.z; dL_dopa += (bq.z - ar0) * dLp0;
-          ar1 = last_alpha * lc1 + (1.0f - last_alpha) * ar1; lc1 = bq.w; dL_dopa += (bq.w - ar1) * dLp1;
-          ar2 = last_alpha * lc2 + (1.0f - last_alpha) * ar2; lc2 = blue; dL_dopa += (blue - ar2) * dLp2;
-          val[0] = aT * dLp0; val[1] = aT * dLp1; val[2] = aT * dLp2;
+          // colour and alpha:  accum_rec = last_alpha * last_colour + (1 - last_alpha) * accum_rec  (alpha: last "colour" 1),
+          // dL_dopa = sum_c (colour_c - accum_rec_c) * dL_dpixel_c + (1 - accum_alpha_rec) * dL_dalpha
+          const f32x2 la2 = pack2(last_alpha, last_alpha), om2 = pack2(1.0f - last_alpha, 1.0f - last_alpha);
+          const f32x2 col01 = pack2(bq.z, bq.w), col2o = pack2(cq.x, cq.y);
+          acc01 = fma2(acc01, om2, mul2(last01, la2));
+          acc2a = fma2(acc2a, om2, mul2(last2o, la2));
+          last01 = col01;
+          last2o = col2o;
+          float dL_dopa = hsum2(fma2(sub2(col2o, acc2a), grad2a, mul2(sub2(col01, acc01), grad01)));
+          unpack2(mul2(grad01, pack2(aT, aT)), val[0], val[1]);
+          val[2] = aT * dLp2;
           float dL_ddelx_geo = 0.0f, dL_ddely_geo = 0.0f;
           if constexpr (GEO) {
             const uint32_t at = tail_base + kk * 64;
@@ -320,28 +332,32 @@ blend_bwd_kernel(BlendBwdParams p) {
               val[22] = aT * dLn0; val[23] = aT * dLn1; val[24] = aT * dLn2;
             }
           }
-          accum_alpha_rec = last_alpha + (1.0f - last_alpha) * accum_alpha_rec;
-          dL_dopa += (1.0f - accum_alpha_rec) * dL_dalpha;
           dL_dopa *= T;
           last_alpha = alpha;
           dL_dopa += (-T_final * rcp) * bg_dot_dpixel;
 
           const float dL_dG = bq.y * dL_dopa;
-          const float gdx = G * dx, gdy = G * dy;
+          const f32x2 gd2 = mul2(d2, pack2(G, G));  // (G dx, G dy)
+          float gdx, gdy;
+          unpack2(gd2, gdx, gdy);
           const float dG_ddelx = -gdx * a.z - gdy * a.w;
           const float dG_ddely = -gdy * bq.x - gdx * a.w;
-          const float ax = dL_dG * dG_ddelx, ay = dL_dG * dG_ddely;
+          const f32x2 axy = mul2(pack2(dG_ddelx, dG_ddely), pack2(dL_dG, dL_dG));
           if constexpr (GEO) {
+            float ax, ay;
+            unpack2(axy, ax, ay);
             val[3] = (ax + dL_ddelx_geo) * p.half_w;
             val[4] = (ay + dL_ddely_geo) * p.half_h;
+            val[5] = fabsf(ax * p.half_w) + fabsf(ay * p.half_h);
           } else {
-            val[3] = ax * p.half_w;
-            val[4] = ay * p.half_h;
+            unpack2(mul2(axy, half2), val[3], val[4]);
+            val[5] = fabsf(val[3]) + fabsf(val[4]);
           }
-          val[5] = fabsf(ax * p.half_w) + fabsf(ay * p.half_h);
-          val[6] = -0.5f * gdx * dx * dL_dG;
-          val[7] = -0.5f * gdx * dy * dL_dG;
-          val[8] = -0.5f * gdy * dy * dL_dG;
+          const f32x2 h2 = mul2(gd2, pack2(-0.5f, -0.5f));
+          float hx, hy;
+          unpack2(h2, hx, hy);
+          unpack2(mul2(mul2(h2, d2), pack2(dL_dG, dL_dG)), val[6], val[8]);  // -0.5 G dx dx dL_dG, -0.5 G dy dy dL_dG
+          val[7] = hx * dy * dL_dG;
           val[9] = G * dL_dopa;
         }
         if constexpr (GEOGRAD) {
@@ -359,7 +375,8 @@ blend_bwd_kernel(BlendBwdParams p) {
           sts32<9 * 144>(stage_wr, val[9]);
           __syncwarp();
           const float4 x0 = lds128<0>(stage_rd), x1 = lds128<16>(stage_rd), x2 = lds128<32>(stage_rd);
-          float sum = ((x0.x + x0.y) + (x0.z + x0.w)) + ((x1.x + x1.y) + (x1.z + x1.w)) + ((x2.x + x2.y) + (x2.z + x2.w));
+          float sum = hsum2(add2(add2(add2(pack2(x0.x, x0.y), pack2(x0.z, x0.w)), add2(pack2(x1.x, x1.y), pack2(x1.z, x1.w))),
+                                 add2(pack2(x2.x, x2.y), pack2(x2.z, x2.w))));
           sum += __shfl_down_sync(0xffffffffu, sum, 1) + __shfl_down_sync(0xffffffffu, sum, 2);
           const uint32_t aa = red_base + __float_as_uint(cq.w) * red_mul;
           sts32<0>(aa, lds32<0>(aa) + sum);
