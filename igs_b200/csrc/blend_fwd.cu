@@ -26,7 +26,7 @@ __global__ void __launch_bounds__(256, MINB)
 blend_fwd_kernel(BlendFwdParams p) {
   constexpr bool GEO = COORD || DEPTH || NORMAL;
   // survivors of the current batch: [0,256) head.a {x, y, conic.x, conic.y}; [256,512) head.b {conic.z, opacity, r, g};
-  // [512,768) {blue, list position (bits), tau, -}
+  // [512,768) {blue, 1.0f, list position (bits), tau}  ((blue, 1) is the fp32x2 multiplicand of (C2, weight))
   __shared__ float4 s_rec[BLEND_BATCH * 3];
   __shared__ float4 s_t[GEO ? BLEND_BATCH * 4 : 1];  // tails of the survivors
   __shared__ uint32_t s_gid[BLEND_BATCH];
@@ -60,10 +60,14 @@ blend_fwd_kernel(BlendFwdParams p) {
 
   float T = 1.0f;
   uint32_t last_contributor = 0, max_contributor = 0xFFFFFFFFu;
-  float C0 = 0, C1 = 0, C2 = 0, weight = 0;
-  float Co0 = 0, Co1 = 0, Co2 = 0, mCo0 = 0, mCo1 = 0, mCo2 = 0;
-  float Depth = 0, mDepth = 0;
-  float N0 = 0, N1 = 0, N2 = 0;
+  // Accumulators kept as fp32x2 pairs: one FFMA2 updates two of them (the kernel is issue bound); every element is
+  // still one fused multiply-add with the rounding of the scalar instruction it replaces.
+  f32x2 C01 = pack2(0.0f, 0.0f), C2w = pack2(0.0f, 0.0f);    // (C0, C1), (C2, weight)
+  f32x2 Co0D = pack2(0.0f, 0.0f), Co12 = pack2(0.0f, 0.0f);  // (Co0, Depth), (Co1, Co2)
+  f32x2 N01 = pack2(0.0f, 0.0f);
+  float N2 = 0;
+  float mCo0 = 0, mCo1 = 0, mCo2 = 0, mDepth = 0;
+  const f32x2 pix2 = pack2(pixfx, pixfy);
 
   for (uint32_t start = range.x; start < range.y; start += BLEND_BATCH) {
     if (__syncthreads_count(done != 0) == 256) break;
@@ -95,7 +99,7 @@ blend_fwd_kernel(BlendFwdParams p) {
       s_rec[k] = ha;
       s_rec[BLEND_BATCH + k] = hb;
       // blue lives in the tail record; 1-based list position = the reference's `contributor`
-      s_rec[2 * BLEND_BATCH + k] = make_float4(p.tail[gid].a.x, __uint_as_float(j - range.x + 1), tau, 0.0f);
+      s_rec[2 * BLEND_BATCH + k] = make_float4(p.tail[gid].a.x, 1.0f, __uint_as_float(j - range.x + 1), tau);
       s_gid[k] = gid;
     }
     __syncthreads();
@@ -116,7 +120,7 @@ blend_fwd_kernel(BlendFwdParams p) {
           const uint32_t ak = rec_base + k * 16;
           float4 a = lds128<0>(ak);
           float4 b = lds128<BLEND_BATCH * 16>(ak);
-          float tk = lds32<BLEND_BATCH * 32 + 8>(ak);
+          float tk = lds32<BLEND_BATCH * 32 + 12>(ak);
           hit = block_can_contribute(a.x, a.y, a.z, a.w, b.x, tk, bx0, by0, bx1, by1);
         }
         uint32_t m = __ballot_sync(0xffffffffu, hit);
@@ -127,39 +131,43 @@ blend_fwd_kernel(BlendFwdParams p) {
           const uint32_t ak = rec_base + kk * 16;
           const float4 a = lds128<0>(ak);
           const float4 bq = lds128<BLEND_BATCH * 16>(ak);
-          const float dx = fsub(a.x, pixfx), dy = fsub(a.y, pixfy);
+          float dx, dy;
+          unpack2(sub2(pack2(a.x, a.y), pix2), dx, dy);  // each rounded like fsub()
           const float power = splat_power(dx, dy, a.z, a.w, bq.x);
           if (power > 0.0f) continue;
           const float alpha = fminf(0.99f, fmul(bq.y, expf(power)));
           if (alpha < 1.0f / 255.0f) continue;
-          const float test_T = fmul(T, fsub(1.0f, alpha));
+          float aT, test_T;
+          unpack2(mul2(pack2(alpha, fsub(1.0f, alpha)), pack2(T, T)), aT, test_T);  // fmul(alpha, T), fmul(T, 1 - alpha)
           if (test_T < 0.0001f) { done = 1; continue; }
-          const float aT = fmul(alpha, T);
-          const float2 bp = lds64<BLEND_BATCH * 32>(ak);  // {blue, position}
-          const uint32_t contributor = __float_as_uint(bp.y);
+          const float4 cq = lds128<BLEND_BATCH * 32>(ak);  // {blue, 1, position, tau}
+          const uint32_t contributor = __float_as_uint(cq.z);
           const bool before_median = T > 0.5f;
+          const f32x2 aT2 = pack2(aT, aT);
           if constexpr (GEO) {
             const uint32_t at = tail_base + kk * 64;
             const float4 t0 = lds128<0>(at), t1 = lds128<16>(at), t2 = lds128<32>(at), t3 = lds128<48>(at);
+            float c0 = 0.0f, tt = 0.0f;
             if constexpr (COORD) {
-              float c0 = ffma(dy, t2.w, ffma(dx, t2.z, t1.w));
-              float c1 = ffma(dy, t3.y, ffma(dx, t3.x, t2.x));
-              float c2 = ffma(dy, t3.w, ffma(dx, t3.z, t2.y));
-              Co0 = ffma(aT, c0, Co0); Co1 = ffma(aT, c1, Co1); Co2 = ffma(aT, c2, Co2);
+              c0 = ffma(dy, t2.w, ffma(dx, t2.z, t1.w));
+              const float c1 = ffma(dy, t3.y, ffma(dx, t3.x, t2.x));
+              const float c2 = ffma(dy, t3.w, ffma(dx, t3.z, t2.y));
+              Co12 = fma2(aT2, pack2(c1, c2), Co12);
               if (before_median) { mCo0 = c0; mCo1 = c1; mCo2 = c2; }
             }
             if constexpr (DEPTH) {
-              float tt = t0.y + (t0.z * dx + t0.w * dy);
-              Depth += tt * aT;
+              tt = t0.y + (t0.z * dx + t0.w * dy);
               if (before_median) mDepth = tt;
             }
+            if constexpr (COORD || DEPTH) Co0D = fma2(aT2, pack2(c0, tt), Co0D);
             if constexpr (NORMAL) {
-              N0 += t1.x * aT; N1 += t1.y * aT; N2 += t1.z * aT;
+              N01 = fma2(aT2, pack2(t1.x, t1.y), N01);
+              N2 = ffma(t1.z, aT, N2);
             }
             if (before_median) max_contributor = contributor;
           }
-          C0 = ffma(aT, bq.z, C0); C1 = ffma(aT, bq.w, C1); C2 = ffma(aT, bp.x, C2);
-          weight += aT;
+          C01 = fma2(aT2, pack2(bq.z, bq.w), C01);
+          C2w = fma2(aT2, pack2(cq.x, cq.y), C2w);  // C2 += aT * blue, weight += aT * 1
           T = test_T;
           last_contributor = contributor;
         }
@@ -168,6 +176,12 @@ blend_fwd_kernel(BlendFwdParams p) {
     }
   }
 
+  float C0, C1, C2, weight, Co0, Co1, Co2, Depth, N0, N1;
+  unpack2(C01, C0, C1);
+  unpack2(C2w, C2, weight);
+  unpack2(Co0D, Co0, Depth);
+  unpack2(Co12, Co1, Co2);
+  unpack2(N01, N0, N1);
   if (inside) {
     p.n_contrib[(size_t)v * 2 * N + pix_id] = last_contributor;
     p.n_contrib[(size_t)v * 2 * N + N + pix_id] = max_contributor;
