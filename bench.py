@@ -371,6 +371,33 @@ def main():
     ms_fwd, _ = timed(fwd_only, max(3, args.steps // 2), 2)
     fwd_mpix = V * N / 1e6 / (ms_fwd / 1e3)
 
+    # ---- (2a) work counters (outside any timed region): E = evaluated (pixel, instance) pairs = sum of n_contrib[0]
+    # (SURVEY 8d), R = instances; and, for N > 1, that every rank holds bit-identical parameters after the steps ----
+    work = None
+    if Vl:
+        with torch.no_grad():
+            sc_a, rot_a, op_a = _C.activate_forward(state.param("scaling"), state.param("rotation"), state.param("opacity"))
+            e_ = torch.empty(0, device=dev)
+            o = _C.rasterize_views(st.bg, state.param("xyz"), e_, op_a, sc_a, rot_a, 1.0, e_, st.viewmatrices, st.projmatrices,
+                                   st.tanfovx, st.tanfovy, 0.0, H, W, state.param("shs"), 3, st.campos, False, True, True, False)
+            dec = _C.decode_buffers(P, Vl, o[0], H, W, o[9], o[10], o[11])
+            E_local = dec[3].view(Vl, 2, H * W)[:, 0].to(torch.int64).sum()
+            R_cnt = torch.tensor(int(o[0]), device=dev, dtype=torch.int64)
+            del o, dec
+    else:
+        E_local = torch.zeros((), device=dev, dtype=torch.int64)
+        R_cnt = torch.zeros((), device=dev, dtype=torch.int64)
+    cs = state.flat.view(torch.int32).to(torch.int64).sum()
+    identical = None
+    if world > 1:
+        pack = torch.stack([E_local, R_cnt])
+        dist.all_reduce(pack)
+        E_local, R_cnt = pack[0], pack[1]
+        css = [torch.zeros_like(cs) for _ in range(world)]
+        dist.all_gather(css, cs)
+        identical = bool(all(int(c) == int(css[0]) for c in css))
+    work = {"instances_R": int(R_cnt), "evaluated_pairs_E": int(E_local), "params_identical_across_ranks": identical}
+
     # ---- (2b) the exchange step alone (packed-gradient all-reduce), for the scaling analysis ----
     allreduce_ms = None
     if world > 1:
@@ -466,7 +493,7 @@ def main():
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "fwd_mpix_s": fwd_mpix, "fwd_ms": ms_fwd, "loss": loss_val, "loss_impl": loss_impl,
         "num_rendered_rank0": int(R_local), "allreduce_ms": allreduce_ms,
-        "allreduce_bytes": int(state.grad.numel() * 4), "per_rank": per_rank, "view_assignment": assignment, "stages": stage_report, "ref_cuda": ref_cuda,
+        "allreduce_bytes": int(state.grad.numel() * 4), "per_rank": per_rank, "view_assignment": assignment, "work": work, "stages": stage_report, "ref_cuda": ref_cuda,
     }
     print(json.dumps(line), flush=True)
     if world > 1:
@@ -521,7 +548,7 @@ def time_reference_cuda(cfg, cams, sc, gt_dev, dev, loss_impl="torch", steps=3):
 
     init = [q.detach().clone() for q in params]
 
-    def one_step(fwd_only=False):
+    def one_step(fwd_only=False, per_view_adam=False):
         tot = 0.0
         with torch.no_grad():
             for q, q0 in zip(params, init):
@@ -537,10 +564,13 @@ def time_reference_cuda(cfg, cams, sc, gt_dev, dev, loss_impl="torch", steps=3):
                 means3D=xyz, means2D=m2, opacities=torch.sigmoid(ol), shs=sh, scales=torch.exp(ls), rotations=F.normalize(rot))
             if fwd_only:
                 continue
-            loss = refine.refine_loss_torch(outs[0].unsqueeze(0), gt_dev[v:v + 1]).sum() / V
+            loss = refine.refine_loss_torch(outs[0].unsqueeze(0), gt_dev[v:v + 1]).sum() / (1 if per_view_adam else V)
             loss.backward()
             tot = loss
-        if not fwd_only:
+            if per_view_adam:   # the reference's own schedule (infer_batch.py:279-324): one Adam step per view
+                opt.step()
+                opt.zero_grad(set_to_none=True)
+        if not fwd_only and not per_view_adam:
             opt.step()
             opt.zero_grad(set_to_none=True)
         return tot
@@ -557,11 +587,20 @@ def time_reference_cuda(cfg, cams, sc, gt_dev, dev, loss_impl="torch", steps=3):
         for _ in range(steps):
             one_step(fwd_only=True)
     e2.record()
+    one_step(per_view_adam=True)
+    e3, e4 = (torch.cuda.Event(enable_timing=True) for _ in range(2))
+    e3.record()
+    for _ in range(steps):
+        one_step(per_view_adam=True)
+    e4.record()
     torch.cuda.synchronize()
     ms = e0.elapsed_time(e1) / steps
     ms_f = e1.elapsed_time(e2) / steps
     return {"ms_per_step": ms, "fwd_ms": ms_f, "fwd_mpix_s": V * W * H / 1e6 / (ms_f / 1e3), "steps": steps,
-            "schedule": "V views accumulated, one torch Adam step; torch L1+SSIM loss; reference rasterizer sm_100a build"}
+            "schedule": "V views accumulated, one torch Adam step; torch L1+SSIM loss; reference rasterizer sm_100a build",
+            "ms_per_V_single_view_iterations": e3.elapsed_time(e4) / steps,
+            "schedule_single_view": "the reference's own loop: V sequential 1-view iterations, each with its own "
+                                    "torch Adam step (infer_batch.py:279-324)"}
 
 
 if __name__ == "__main__":

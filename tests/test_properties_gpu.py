@@ -20,7 +20,7 @@ def _scene(cfg_name, dev, view=0):
     return cfg, t, cam
 
 
-@pytest.mark.parametrize("cfg_name,view", [("C2", 0), ("C3", 7)])
+@pytest.mark.parametrize("cfg_name,view", [("C2", 0), ("C3", 7), ("C4", 5), ("C5", 3)])
 def test_binning_invariants_full_size(cuda_dev, native, cfg_name, view):
     cfg, t, cam = _scene(cfg_name, cuda_dev, view)
     P, W, H = cfg["P"], cfg["W"], cfg["H"]
