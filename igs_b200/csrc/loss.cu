@@ -11,6 +11,7 @@
 //           padding is zero, so the adjoint of the convolution is the same convolution), combined with the L1 sign.
 // The scalar loss is reduced deterministically: per-block partial sums in double, then one final block.
 #include "common.cuh"
+#include "blend_common.cuh"
 #include "kernels.cuh"
 
 namespace igs {
@@ -36,16 +37,23 @@ struct LossParams {
   double* partial;         // [gridDim.x*gridDim.y*gridDim.z]
 };
 
-__device__ __forceinline__ float ld_pad(const float* __restrict__ p, int x, int y, int W, int H) {
-  return (x >= 0 && x < W && y >= 0 && y < H) ? p[(size_t)y * W + x] : 0.0f;
-}
-
-// Register-tiled separable filter helpers.  Shared input tiles have a row stride of LOSS_TS floats (16-B aligned
-// rows); the horizontal pass gives each thread 4 adjacent output columns of one row (14 inputs, loaded as three
-// 16-B and one 8-B shared loads), the vertical pass gives each thread 4 adjacent output rows of one column
-// (14 inputs reused across the 4 outputs) — ~4x fewer shared-memory instructions than one output per thread.
+// Register-tiled separable filters on fp32x2 pairs.  The kernels are instruction-issue bound (ncu: 77 % / 56 %
+// issue-active, DRAM 15-18 %), so the five (pass 1) / three (pass 2) filtered quantities are carried as packed pairs
+// — (mu1, mu2), (E11, E22) and E12;  (dmu1, dE11) and dE12 — and one FFMA2 advances two of them.  Shared tiles hold
+// the pairs interleaved (row stride LOSS_TS pairs, 16-B aligned rows).  The horizontal pass gives each thread 4
+// adjacent output columns of one row (14 input pairs, seven 16-B shared loads), the vertical pass 4 adjacent output
+// rows of one column (14 inputs reused across the 4 outputs).  Every element is still one fused multiply-add per tap,
+// rounded exactly like the scalar instruction.
 #define LOSS_TS 44
 
+__device__ __forceinline__ void load14_pairs(const float2* row, f32x2 (&x)[14]) {
+#pragma unroll
+  for (int i = 0; i < 7; i++) {
+    const float4 a = *reinterpret_cast<const float4*>(row + 2 * i);
+    x[2 * i] = pack2(a.x, a.y);
+    x[2 * i + 1] = pack2(a.z, a.w);
+  }
+}
 __device__ __forceinline__ void load14(const float* row, float (&x)[14]) {
   const float4 a = *reinterpret_cast<const float4*>(row), b = *reinterpret_cast<const float4*>(row + 4),
                c = *reinterpret_cast<const float4*>(row + 8);
@@ -53,12 +61,20 @@ __device__ __forceinline__ void load14(const float* row, float (&x)[14]) {
   x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w; x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
   x[8] = c.x; x[9] = c.y; x[10] = c.z; x[11] = c.w; x[12] = d.x; x[13] = d.y;
 }
+__device__ __forceinline__ void store4_pairs(float2* dst, const f32x2 (&o)[4]) {
+  float a, b, c, d;
+  unpack2(o[0], a, b); unpack2(o[1], c, d);
+  *reinterpret_cast<float4*>(dst) = make_float4(a, b, c, d);
+  unpack2(o[2], a, b); unpack2(o[3], c, d);
+  *reinterpret_cast<float4*>(dst + 2) = make_float4(a, b, c, d);
+}
 
 __global__ void __launch_bounds__(256)
 loss_pass1_kernel(LossParams p) {
-  __shared__ __align__(16) float sx[LOSS_TH][LOSS_TS];
-  __shared__ __align__(16) float sy[LOSS_TH][LOSS_TS];
-  __shared__ __align__(16) float hb[5][LOSS_TH][LOSS_BX];
+  __shared__ __align__(16) float2 sxy[LOSS_TH][LOSS_TS];           // (pred, gt)
+  __shared__ __align__(16) float2 hbA[LOSS_TH][LOSS_BX];           // horizontally filtered (x, y)
+  __shared__ __align__(16) float2 hbB[LOSS_TH][LOSS_BX];           // (x^2, y^2)
+  __shared__ __align__(16) float hbC[LOSS_TH][LOSS_BX];            // x y
   __shared__ double red[8];
   const int plane = blockIdx.z;
   const float* __restrict__ X = p.pred + (size_t)plane * p.H * p.W;
@@ -73,32 +89,43 @@ loss_pass1_kernel(LossParams p) {
     for (int tx = tid & 31; tx < LOSS_TW; tx += 32) {
       const int gx = x0 + tx - LOSS_R;
       const bool ok = rowok && gx >= 0 && gx < p.W;
-      sx[ty][tx] = ok ? X[ro + gx] : 0.0f;
-      sy[ty][tx] = ok ? Y[ro + gx] : 0.0f;
+      sxy[ty][tx] = make_float2(ok ? X[ro + gx] : 0.0f, ok ? Y[ro + gx] : 0.0f);
     }
   }
   __syncthreads();
+  f32x2 w2[11];
+#pragma unroll
+  for (int k = 0; k < 11; k++) w2[k] = pack2(p.win[k], p.win[k]);
   // horizontal: task = (row r, column group cg of 4 outputs)
   if (tid < LOSS_TH * (LOSS_BX / 4)) {
     const int r = tid / (LOSS_BX / 4), cg = tid - r * (LOSS_BX / 4);
-    float xv[14], yv[14];
-    load14(&sx[r][cg * 4], xv);
-    load14(&sy[r][cg * 4], yv);
-    float o[5][4];
+    f32x2 v[14], sq[14];
+    float pr[14];
+    load14_pairs(&sxy[r][cg * 4], v);
+#pragma unroll
+    for (int k = 0; k < 14; k++) {
+      float xx, yy;
+      unpack2(v[k], xx, yy);
+      sq[k] = mul2(v[k], v[k]);
+      pr[k] = xx * yy;
+    }
+    f32x2 oA[4], oB[4];
+    float oC[4];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      float a0 = 0, a1 = 0, a2 = 0, a3 = 0, a4 = 0;
+      f32x2 a = pack2(0.0f, 0.0f), b = pack2(0.0f, 0.0f);
+      float c = 0.0f;
 #pragma unroll
       for (int k = 0; k < 11; k++) {
-        const float w = p.win[k], xx = xv[j + k], yy = yv[j + k];
-        a0 = fmaf(w, xx, a0); a1 = fmaf(w, yy, a1);
-        a2 = fmaf(w, xx * xx, a2); a3 = fmaf(w, yy * yy, a3); a4 = fmaf(w, xx * yy, a4);
+        a = fma2(w2[k], v[j + k], a);
+        b = fma2(w2[k], sq[j + k], b);
+        c = fmaf(p.win[k], pr[j + k], c);
       }
-      o[0][j] = a0; o[1][j] = a1; o[2][j] = a2; o[3][j] = a3; o[4][j] = a4;
+      oA[j] = a; oB[j] = b; oC[j] = c;
     }
-#pragma unroll
-    for (int q = 0; q < 5; q++)
-      *reinterpret_cast<float4*>(&hb[q][r][cg * 4]) = make_float4(o[q][0], o[q][1], o[q][2], o[q][3]);
+    store4_pairs(&hbA[r][cg * 4], oA);
+    store4_pairs(&hbB[r][cg * 4], oB);
+    *reinterpret_cast<float4*>(&hbC[r][cg * 4]) = make_float4(oC[0], oC[1], oC[2], oC[3]);
   }
   __syncthreads();
   // vertical + SSIM + partials: task = (column c, row group rg of 4 outputs)
@@ -106,18 +133,37 @@ loss_pass1_kernel(LossParams p) {
   const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
   if (tid < LOSS_BX * (LOSS_BY / 4)) {
     const int c = tid % LOSS_BX, rg = tid / LOSS_BX;
-    float m[5][4];
+    f32x2 mA[4], mB[4];
+    float mC[4];
+    {
+      f32x2 in[14];
 #pragma unroll
-    for (int q = 0; q < 5; q++) {
-      float in[14];
-#pragma unroll
-      for (int k = 0; k < 14; k++) in[k] = hb[q][rg * 4 + k][c];
+      for (int k = 0; k < 14; k++) { const float2 t = hbA[rg * 4 + k][c]; in[k] = pack2(t.x, t.y); }
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        float a = 0;
+        f32x2 a = pack2(0.0f, 0.0f);
 #pragma unroll
-        for (int k = 0; k < 11; k++) a = fmaf(p.win[k], in[j + k], a);
-        m[q][j] = a;
+        for (int k = 0; k < 11; k++) a = fma2(w2[k], in[j + k], a);
+        mA[j] = a;
+      }
+#pragma unroll
+      for (int k = 0; k < 14; k++) { const float2 t = hbB[rg * 4 + k][c]; in[k] = pack2(t.x, t.y); }
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        f32x2 a = pack2(0.0f, 0.0f);
+#pragma unroll
+        for (int k = 0; k < 11; k++) a = fma2(w2[k], in[j + k], a);
+        mB[j] = a;
+      }
+      float ins[14];
+#pragma unroll
+      for (int k = 0; k < 14; k++) ins[k] = hbC[rg * 4 + k][c];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        float a = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 11; k++) a = fmaf(p.win[k], ins[j + k], a);
+        mC[j] = a;
       }
     }
     const int gx = x0 + c;
@@ -125,7 +171,10 @@ loss_pass1_kernel(LossParams p) {
     for (int j = 0; j < 4; j++) {
       const int gy = y0 + rg * 4 + j;
       if (gx >= p.W || gy >= p.H) continue;
-      const float mu1 = m[0][j], mu2 = m[1][j], e11 = m[2][j], e22 = m[3][j], e12 = m[4][j];
+      float mu1, mu2, e11, e22;
+      unpack2(mA[j], mu1, mu2);
+      unpack2(mB[j], e11, e22);
+      const float e12 = mC[j];
       const float mu1_sq = mu1 * mu1, mu2_sq = mu2 * mu2, mu12 = mu1 * mu2;
       const float s1 = e11 - mu1_sq, s2 = e22 - mu2_sq, s12 = e12 - mu12;
       const float A = 2.0f * mu12 + C1, B = 2.0f * s12 + C2, Cc = mu1_sq + mu2_sq + C1, D = s1 + s2 + C2;
@@ -137,8 +186,8 @@ loss_pass1_kernel(LossParams p) {
       const float d12 = 2.0f * A * inv;
       const size_t o = (size_t)plane * p.H * p.W + (size_t)gy * p.W + gx;
       p.dmu1[o] = dmu1; p.dE11[o] = d11; p.dE12[o] = d12;
-      const float xv = sx[rg * 4 + j + LOSS_R][c + LOSS_R], yv = sy[rg * 4 + j + LOSS_R][c + LOSS_R];
-      acc += (double)(p.lambda * fabsf(xv - yv)) - (double)((1.0f - p.lambda) * ssim);
+      const float2 xy = sxy[rg * 4 + j + LOSS_R][c + LOSS_R];
+      acc += (double)(p.lambda * fabsf(xy.x - xy.y)) - (double)((1.0f - p.lambda) * ssim);
     }
   }
   // block reduce (fixed order)
@@ -155,10 +204,10 @@ loss_pass1_kernel(LossParams p) {
 
 __global__ void __launch_bounds__(256)
 loss_pass2_kernel(LossParams p) {
-  __shared__ __align__(16) float s0[LOSS_TH][LOSS_TS];
-  __shared__ __align__(16) float s1[LOSS_TH][LOSS_TS];
-  __shared__ __align__(16) float s2[LOSS_TH][LOSS_TS];
-  __shared__ __align__(16) float hb[3][LOSS_TH][LOSS_BX];
+  __shared__ __align__(16) float2 s01[LOSS_TH][LOSS_TS];           // (dS/dmu1, dS/dE11)
+  __shared__ __align__(16) float s2[LOSS_TH][LOSS_TS];             // dS/dE12
+  __shared__ __align__(16) float2 hb01[LOSS_TH][LOSS_BX];
+  __shared__ __align__(16) float hb2[LOSS_TH][LOSS_BX];
   const int plane = blockIdx.z;
   const size_t po = (size_t)plane * p.H * p.W;
   const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
@@ -170,48 +219,61 @@ loss_pass2_kernel(LossParams p) {
     for (int tx = tid & 31; tx < LOSS_TW; tx += 32) {
       const int gx = x0 + tx - LOSS_R;
       const bool ok = rowok && gx >= 0 && gx < p.W;
-      s0[ty][tx] = ok ? p.dmu1[ro + gx] : 0.0f;
-      s1[ty][tx] = ok ? p.dE11[ro + gx] : 0.0f;
+      s01[ty][tx] = make_float2(ok ? p.dmu1[ro + gx] : 0.0f, ok ? p.dE11[ro + gx] : 0.0f);
       s2[ty][tx] = ok ? p.dE12[ro + gx] : 0.0f;
     }
   }
   __syncthreads();
+  f32x2 w2[11];
+#pragma unroll
+  for (int k = 0; k < 11; k++) w2[k] = pack2(p.win[k], p.win[k]);
   if (tid < LOSS_TH * (LOSS_BX / 4)) {
     const int r = tid / (LOSS_BX / 4), cg = tid - r * (LOSS_BX / 4);
-    float v0[14], v1[14], v2[14];
-    load14(&s0[r][cg * 4], v0);
-    load14(&s1[r][cg * 4], v1);
-    load14(&s2[r][cg * 4], v2);
-    float o[3][4];
+    f32x2 v[14];
+    float u[14];
+    load14_pairs(&s01[r][cg * 4], v);
+    load14(&s2[r][cg * 4], u);
+    f32x2 o01[4];
+    float o2[4];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
-      float a0 = 0, a1 = 0, a2 = 0;
+      f32x2 a = pack2(0.0f, 0.0f);
+      float c = 0.0f;
 #pragma unroll
       for (int k = 0; k < 11; k++) {
-        const float w = p.win[k];
-        a0 = fmaf(w, v0[j + k], a0); a1 = fmaf(w, v1[j + k], a1); a2 = fmaf(w, v2[j + k], a2);
+        a = fma2(w2[k], v[j + k], a);
+        c = fmaf(p.win[k], u[j + k], c);
       }
-      o[0][j] = a0; o[1][j] = a1; o[2][j] = a2;
+      o01[j] = a; o2[j] = c;
     }
-#pragma unroll
-    for (int q = 0; q < 3; q++)
-      *reinterpret_cast<float4*>(&hb[q][r][cg * 4]) = make_float4(o[q][0], o[q][1], o[q][2], o[q][3]);
+    store4_pairs(&hb01[r][cg * 4], o01);
+    *reinterpret_cast<float4*>(&hb2[r][cg * 4]) = make_float4(o2[0], o2[1], o2[2], o2[3]);
   }
   __syncthreads();
   if (tid < LOSS_BX * (LOSS_BY / 4)) {
     const int c = tid % LOSS_BX, rg = tid / LOSS_BX;
-    float m[3][4];
+    f32x2 m01[4];
+    float m2[4];
+    {
+      f32x2 in[14];
 #pragma unroll
-    for (int q = 0; q < 3; q++) {
-      float in[14];
-#pragma unroll
-      for (int k = 0; k < 14; k++) in[k] = hb[q][rg * 4 + k][c];
+      for (int k = 0; k < 14; k++) { const float2 t = hb01[rg * 4 + k][c]; in[k] = pack2(t.x, t.y); }
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        float a = 0;
+        f32x2 a = pack2(0.0f, 0.0f);
 #pragma unroll
-        for (int k = 0; k < 11; k++) a = fmaf(p.win[k], in[j + k], a);
-        m[q][j] = a;
+        for (int k = 0; k < 11; k++) a = fma2(w2[k], in[j + k], a);
+        m01[j] = a;
+      }
+      float ins[14];
+#pragma unroll
+      for (int k = 0; k < 14; k++) ins[k] = hb2[rg * 4 + k][c];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        float a = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 11; k++) a = fmaf(p.win[k], ins[j + k], a);
+        m2[j] = a;
       }
     }
     const int gx = x0 + c;
@@ -221,7 +283,9 @@ loss_pass2_kernel(LossParams p) {
       if (gx >= p.W || gy >= p.H) continue;
       const size_t o = po + (size_t)gy * p.W + gx;
       const float xv = p.pred[o], yv = p.gt[o];
-      const float dssim = m[0][j] + 2.0f * xv * m[1][j] + yv * m[2][j];
+      float g0, g1;
+      unpack2(m01[j], g0, g1);
+      const float dssim = g0 + 2.0f * xv * g1 + yv * m2[j];
       const float d = xv - yv;
       const float sgn = (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f);   // torch: sign(0) = 0
       p.dpred[o] = (p.lambda * sgn - (1.0f - p.lambda) * dssim) * p.inv_n;
