@@ -17,10 +17,11 @@
 namespace igs {
 
 #define LOSS_BX 32
-#define LOSS_BY 16
+#define LOSS_BY 32
 #define LOSS_R 5
-#define LOSS_TW (LOSS_BX + 2 * LOSS_R)  // 42
-#define LOSS_TH (LOSS_BY + 2 * LOSS_R)  // 26
+#define LOSS_TH (LOSS_BY + 2 * LOSS_R)  // 42 rows: tile + halo
+#define LOSS_TC 48                      // staged columns: x0-8 .. x0+39 (16-B aligned superset of the 42-column halo)
+#define LOSS_X0 8                       // staged column of image column x0
 
 struct LossParams {
   int planes, H, W;        // planes = V*3
@@ -37,29 +38,30 @@ struct LossParams {
   double* partial;         // [gridDim.x*gridDim.y*gridDim.z]
 };
 
-// Register-tiled separable filters on fp32x2 pairs.  The kernels are instruction-issue bound (ncu: 77 % / 56 %
-// issue-active, DRAM 15-18 %), so the five (pass 1) / three (pass 2) filtered quantities are carried as packed pairs
-// — (mu1, mu2), (E11, E22) and E12;  (dmu1, dE11) and dE12 — and one FFMA2 advances two of them.  Shared tiles hold
-// the pairs interleaved (row stride LOSS_TS pairs, 16-B aligned rows).  The horizontal pass gives each thread 4
-// adjacent output columns of one row (14 input pairs, seven 16-B shared loads), the vertical pass 4 adjacent output
-// rows of one column (14 inputs reused across the 4 outputs).  Every element is still one fused multiply-add per tap,
-// rounded exactly like the scalar instruction.
-#define LOSS_TS 44
-
-__device__ __forceinline__ void load14_pairs(const float2* row, f32x2 (&x)[14]) {
+// Register-tiled separable filters on fp32x2 pairs.  The kernels are instruction-issue bound (ncu: DRAM 15-18 % of
+// peak), so
+//  * the five (pass 1) / three (pass 2) filtered quantities are carried as packed pairs — (mu1, mu2), (E11, E22) and
+//    E12;  (dmu1, dE11) and dE12 — and one FFMA2 advances two of them; every element is still one fused multiply-add
+//    per tap, rounded exactly like the scalar instruction;
+//  * the tile + halo is staged with 16-byte global loads of an aligned 48-column superset (VEC: W % 4 == 0 and
+//    16-byte aligned planes; each float4 is then entirely inside or entirely outside the image), which cut the
+//    staging loop from 30-48 % of all executed instructions to a few percent;
+//  * the horizontal pass gives each thread 4 adjacent output columns of one row (16 input pairs from eight 16-B
+//    shared loads), the vertical pass 4 adjacent output rows of one column (14 inputs reused across the 4 outputs).
+__device__ __forceinline__ void load16_pairs(const float2* row, f32x2 (&x)[16]) {
 #pragma unroll
-  for (int i = 0; i < 7; i++) {
+  for (int i = 0; i < 8; i++) {
     const float4 a = *reinterpret_cast<const float4*>(row + 2 * i);
     x[2 * i] = pack2(a.x, a.y);
     x[2 * i + 1] = pack2(a.z, a.w);
   }
 }
-__device__ __forceinline__ void load14(const float* row, float (&x)[14]) {
-  const float4 a = *reinterpret_cast<const float4*>(row), b = *reinterpret_cast<const float4*>(row + 4),
-               c = *reinterpret_cast<const float4*>(row + 8);
-  const float2 d = *reinterpret_cast<const float2*>(row + 12);
-  x[0] = a.x; x[1] = a.y; x[2] = a.z; x[3] = a.w; x[4] = b.x; x[5] = b.y; x[6] = b.z; x[7] = b.w;
-  x[8] = c.x; x[9] = c.y; x[10] = c.z; x[11] = c.w; x[12] = d.x; x[13] = d.y;
+__device__ __forceinline__ void load20(const float* row, float (&x)[20]) {
+#pragma unroll
+  for (int i = 0; i < 5; i++) {
+    const float4 a = *reinterpret_cast<const float4*>(row + 4 * i);
+    x[4 * i] = a.x; x[4 * i + 1] = a.y; x[4 * i + 2] = a.z; x[4 * i + 3] = a.w;
+  }
 }
 __device__ __forceinline__ void store4_pairs(float2* dst, const f32x2 (&o)[4]) {
   float a, b, c, d;
@@ -69,41 +71,81 @@ __device__ __forceinline__ void store4_pairs(float2* dst, const f32x2 (&o)[4]) {
   *reinterpret_cast<float4*>(dst + 2) = make_float4(a, b, c, d);
 }
 
+// Stage rows [y0-5, y0+37) x columns [x0-8, x0+40) of two planes A, B as interleaved pairs (zero outside the image).
+template <bool VEC>
+__device__ __forceinline__ void stage_pairs(float2 (*dst)[LOSS_TC], const float* __restrict__ A,
+                                            const float* __restrict__ B, int x0, int y0, int W, int H, int tid) {
+  if constexpr (VEC) {
+    for (int t = tid; t < LOSS_TH * (LOSS_TC / 4); t += 256) {
+      const int ty = t / (LOSS_TC / 4), g = t - ty * (LOSS_TC / 4);
+      const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + 4 * g;
+      float4 a = make_float4(0, 0, 0, 0), b = a;
+      if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+        const uint32_t o = (uint32_t)gy * (uint32_t)W + (uint32_t)gx;
+        a = *reinterpret_cast<const float4*>(A + o);
+        b = *reinterpret_cast<const float4*>(B + o);
+      }
+      float4* d = reinterpret_cast<float4*>(&dst[ty][4 * g]);
+      d[0] = make_float4(a.x, b.x, a.y, b.y);
+      d[1] = make_float4(a.z, b.z, a.w, b.w);
+    }
+  } else {
+    for (int t = tid; t < LOSS_TH * LOSS_TC; t += 256) {
+      const int ty = t / LOSS_TC, tx = t - ty * LOSS_TC;
+      const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + tx;
+      const bool ok = gy >= 0 && gy < H && gx >= 0 && gx < W;
+      const uint32_t o = ok ? (uint32_t)gy * (uint32_t)W + (uint32_t)gx : 0u;
+      dst[ty][tx] = make_float2(ok ? A[o] : 0.0f, ok ? B[o] : 0.0f);
+    }
+  }
+}
+template <bool VEC>
+__device__ __forceinline__ void stage_scalar(float (*dst)[LOSS_TC], const float* __restrict__ A, int x0, int y0, int W,
+                                             int H, int tid) {
+  if constexpr (VEC) {
+    for (int t = tid; t < LOSS_TH * (LOSS_TC / 4); t += 256) {
+      const int ty = t / (LOSS_TC / 4), g = t - ty * (LOSS_TC / 4);
+      const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + 4 * g;
+      float4 a = make_float4(0, 0, 0, 0);
+      if (gy >= 0 && gy < H && gx >= 0 && gx < W) a = *reinterpret_cast<const float4*>(A + (uint32_t)gy * (uint32_t)W + (uint32_t)gx);
+      *reinterpret_cast<float4*>(&dst[ty][4 * g]) = a;
+    }
+  } else {
+    for (int t = tid; t < LOSS_TH * LOSS_TC; t += 256) {
+      const int ty = t / LOSS_TC, tx = t - ty * LOSS_TC;
+      const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + tx;
+      const bool ok = gy >= 0 && gy < H && gx >= 0 && gx < W;
+      dst[ty][tx] = ok ? A[(uint32_t)gy * (uint32_t)W + (uint32_t)gx] : 0.0f;
+    }
+  }
+}
+
+template <bool VEC>
 __global__ void __launch_bounds__(256)
 loss_pass1_kernel(LossParams p) {
-  __shared__ __align__(16) float2 sxy[LOSS_TH][LOSS_TS];           // (pred, gt)
+  __shared__ __align__(16) float2 sxy[LOSS_TH][LOSS_TC];           // (pred, gt)
   __shared__ __align__(16) float2 hbA[LOSS_TH][LOSS_BX];           // horizontally filtered (x, y)
   __shared__ __align__(16) float2 hbB[LOSS_TH][LOSS_BX];           // (x^2, y^2)
   __shared__ __align__(16) float hbC[LOSS_TH][LOSS_BX];            // x y
   __shared__ double red[8];
   const int plane = blockIdx.z;
-  const float* __restrict__ X = p.pred + (size_t)plane * p.H * p.W;
-  const float* __restrict__ Y = p.gt + (size_t)plane * p.H * p.W;
+  const size_t po = (size_t)plane * p.H * p.W;
   const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
   const int tid = threadIdx.x;
-  // tile + halo, one row per warp iteration (no index division; zero padding outside the image)
-  for (int ty = tid >> 5; ty < LOSS_TH; ty += 8) {
-    const int gy = y0 + ty - LOSS_R;
-    const bool rowok = gy >= 0 && gy < p.H;
-    const size_t ro = (size_t)(rowok ? gy : 0) * p.W;
-    for (int tx = tid & 31; tx < LOSS_TW; tx += 32) {
-      const int gx = x0 + tx - LOSS_R;
-      const bool ok = rowok && gx >= 0 && gx < p.W;
-      sxy[ty][tx] = make_float2(ok ? X[ro + gx] : 0.0f, ok ? Y[ro + gx] : 0.0f);
-    }
-  }
+  stage_pairs<VEC>(sxy, p.pred + po, p.gt + po, x0, y0, p.W, p.H, tid);
   __syncthreads();
   f32x2 w2[11];
 #pragma unroll
   for (int k = 0; k < 11; k++) w2[k] = pack2(p.win[k], p.win[k]);
-  // horizontal: task = (row r, column group cg of 4 outputs)
-  if (tid < LOSS_TH * (LOSS_BX / 4)) {
-    const int r = tid / (LOSS_BX / 4), cg = tid - r * (LOSS_BX / 4);
-    f32x2 v[14], sq[14];
-    float pr[14];
-    load14_pairs(&sxy[r][cg * 4], v);
+  // horizontal: task = (row r, column group cg of 4 outputs); taps of output column 4cg+j are staged columns
+  // 4cg+3+j .. 4cg+13+j = v[1+j .. 11+j] of the 16 pairs loaded from the (16-B aligned) column 4cg+2
+  for (int t = tid; t < LOSS_TH * (LOSS_BX / 4); t += 256) {
+    const int r = t / (LOSS_BX / 4), cg = t - r * (LOSS_BX / 4);
+    f32x2 v[16], sq[16];
+    float pr[16];
+    load16_pairs(&sxy[r][cg * 4 + 2], v);
 #pragma unroll
-    for (int k = 0; k < 14; k++) {
+    for (int k = 1; k < 15; k++) {
       float xx, yy;
       unpack2(v[k], xx, yy);
       sq[k] = mul2(v[k], v[k]);
@@ -117,9 +159,9 @@ loss_pass1_kernel(LossParams p) {
       float c = 0.0f;
 #pragma unroll
       for (int k = 0; k < 11; k++) {
-        a = fma2(w2[k], v[j + k], a);
-        b = fma2(w2[k], sq[j + k], b);
-        c = fmaf(p.win[k], pr[j + k], c);
+        a = fma2(w2[k], v[1 + j + k], a);
+        b = fma2(w2[k], sq[1 + j + k], b);
+        c = fmaf(p.win[k], pr[1 + j + k], c);
       }
       oA[j] = a; oB[j] = b; oC[j] = c;
     }
@@ -128,10 +170,10 @@ loss_pass1_kernel(LossParams p) {
     *reinterpret_cast<float4*>(&hbC[r][cg * 4]) = make_float4(oC[0], oC[1], oC[2], oC[3]);
   }
   __syncthreads();
-  // vertical + SSIM + partials: task = (column c, row group rg of 4 outputs)
+  // vertical + SSIM + partials: task = (column c, row group rg of 4 outputs), all 256 threads
   double acc = 0.0;
   const float C1 = 0.01f * 0.01f, C2 = 0.03f * 0.03f;
-  if (tid < LOSS_BX * (LOSS_BY / 4)) {
+  {
     const int c = tid % LOSS_BX, rg = tid / LOSS_BX;
     f32x2 mA[4], mB[4];
     float mC[4];
@@ -167,6 +209,9 @@ loss_pass1_kernel(LossParams p) {
       }
     }
     const int gx = x0 + c;
+    float* __restrict__ o_mu = p.dmu1 + po;
+    float* __restrict__ o_11 = p.dE11 + po;
+    float* __restrict__ o_12 = p.dE12 + po;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int gy = y0 + rg * 4 + j;
@@ -184,9 +229,9 @@ loss_pass1_kernel(LossParams p) {
       const float dmu1 = (2.0f * mu2 * B - 2.0f * mu2 * A) * inv - ssim * (2.0f * mu1 * D - 2.0f * mu1 * Cc) * inv;
       const float d11 = -ssim / D;
       const float d12 = 2.0f * A * inv;
-      const size_t o = (size_t)plane * p.H * p.W + (size_t)gy * p.W + gx;
-      p.dmu1[o] = dmu1; p.dE11[o] = d11; p.dE12[o] = d12;
-      const float2 xy = sxy[rg * 4 + j + LOSS_R][c + LOSS_R];
+      const uint32_t o = (uint32_t)gy * (uint32_t)p.W + (uint32_t)gx;
+      o_mu[o] = dmu1; o_11[o] = d11; o_12[o] = d12;
+      const float2 xy = sxy[rg * 4 + j + LOSS_R][c + LOSS_X0];
       acc += (double)(p.lambda * fabsf(xy.x - xy.y)) - (double)((1.0f - p.lambda) * ssim);
     }
   }
@@ -202,37 +247,29 @@ loss_pass1_kernel(LossParams p) {
   }
 }
 
+template <bool VEC>
 __global__ void __launch_bounds__(256)
 loss_pass2_kernel(LossParams p) {
-  __shared__ __align__(16) float2 s01[LOSS_TH][LOSS_TS];           // (dS/dmu1, dS/dE11)
-  __shared__ __align__(16) float s2[LOSS_TH][LOSS_TS];             // dS/dE12
+  __shared__ __align__(16) float2 s01[LOSS_TH][LOSS_TC];           // (dS/dmu1, dS/dE11)
+  __shared__ __align__(16) float s2[LOSS_TH][LOSS_TC];             // dS/dE12
   __shared__ __align__(16) float2 hb01[LOSS_TH][LOSS_BX];
   __shared__ __align__(16) float hb2[LOSS_TH][LOSS_BX];
   const int plane = blockIdx.z;
   const size_t po = (size_t)plane * p.H * p.W;
   const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
   const int tid = threadIdx.x;
-  for (int ty = tid >> 5; ty < LOSS_TH; ty += 8) {
-    const int gy = y0 + ty - LOSS_R;
-    const bool rowok = gy >= 0 && gy < p.H;
-    const size_t ro = po + (size_t)(rowok ? gy : 0) * p.W;
-    for (int tx = tid & 31; tx < LOSS_TW; tx += 32) {
-      const int gx = x0 + tx - LOSS_R;
-      const bool ok = rowok && gx >= 0 && gx < p.W;
-      s01[ty][tx] = make_float2(ok ? p.dmu1[ro + gx] : 0.0f, ok ? p.dE11[ro + gx] : 0.0f);
-      s2[ty][tx] = ok ? p.dE12[ro + gx] : 0.0f;
-    }
-  }
+  stage_pairs<VEC>(s01, p.dmu1 + po, p.dE11 + po, x0, y0, p.W, p.H, tid);
+  stage_scalar<VEC>(s2, p.dE12 + po, x0, y0, p.W, p.H, tid);
   __syncthreads();
   f32x2 w2[11];
 #pragma unroll
   for (int k = 0; k < 11; k++) w2[k] = pack2(p.win[k], p.win[k]);
-  if (tid < LOSS_TH * (LOSS_BX / 4)) {
-    const int r = tid / (LOSS_BX / 4), cg = tid - r * (LOSS_BX / 4);
-    f32x2 v[14];
-    float u[14];
-    load14_pairs(&s01[r][cg * 4], v);
-    load14(&s2[r][cg * 4], u);
+  for (int t = tid; t < LOSS_TH * (LOSS_BX / 4); t += 256) {
+    const int r = t / (LOSS_BX / 4), cg = t - r * (LOSS_BX / 4);
+    f32x2 v[16];
+    float u[20];
+    load16_pairs(&s01[r][cg * 4 + 2], v);  // taps of output column 4cg+j: v[1+j .. 11+j]
+    load20(&s2[r][cg * 4], u);             //                              u[3+j .. 13+j]
     f32x2 o01[4];
     float o2[4];
 #pragma unroll
@@ -241,8 +278,8 @@ loss_pass2_kernel(LossParams p) {
       float c = 0.0f;
 #pragma unroll
       for (int k = 0; k < 11; k++) {
-        a = fma2(w2[k], v[j + k], a);
-        c = fmaf(p.win[k], u[j + k], c);
+        a = fma2(w2[k], v[1 + j + k], a);
+        c = fmaf(p.win[k], u[3 + j + k], c);
       }
       o01[j] = a; o2[j] = c;
     }
@@ -250,7 +287,7 @@ loss_pass2_kernel(LossParams p) {
     *reinterpret_cast<float4*>(&hb2[r][cg * 4]) = make_float4(o2[0], o2[1], o2[2], o2[3]);
   }
   __syncthreads();
-  if (tid < LOSS_BX * (LOSS_BY / 4)) {
+  {
     const int c = tid % LOSS_BX, rg = tid / LOSS_BX;
     f32x2 m01[4];
     float m2[4];
@@ -277,18 +314,21 @@ loss_pass2_kernel(LossParams p) {
       }
     }
     const int gx = x0 + c;
+    const float* __restrict__ X = p.pred + po;
+    const float* __restrict__ Y = p.gt + po;
+    float* __restrict__ O = p.dpred + po;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int gy = y0 + rg * 4 + j;
       if (gx >= p.W || gy >= p.H) continue;
-      const size_t o = po + (size_t)gy * p.W + gx;
-      const float xv = p.pred[o], yv = p.gt[o];
+      const uint32_t o = (uint32_t)gy * (uint32_t)p.W + (uint32_t)gx;
+      const float xv = X[o], yv = Y[o];
       float g0, g1;
       unpack2(m01[j], g0, g1);
       const float dssim = g0 + 2.0f * xv * g1 + yv * m2[j];
       const float d = xv - yv;
       const float sgn = (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f);   // torch: sign(0) = 0
-      p.dpred[o] = (p.lambda * sgn - (1.0f - p.lambda) * dssim) * p.inv_n;
+      O[o] = (p.lambda * sgn - (1.0f - p.lambda) * dssim) * p.inv_n;
     }
   }
 }
@@ -336,8 +376,17 @@ void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W,
   p.partial = reinterpret_cast<double*>(scratch + off);
   dim3 grid((W + LOSS_BX - 1) / LOSS_BX, (H + LOSS_BY - 1) / LOSS_BY, V * 3);
   count_launch(3);
-  loss_pass1_kernel<<<grid, 256, 0, s>>>(p);
-  loss_pass2_kernel<<<grid, 256, 0, s>>>(p);
+  // 16-byte staging loads need W % 4 == 0 (every float4 entirely inside or outside the image) and aligned planes
+  const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(gt) |
+                                     reinterpret_cast<uintptr_t>(p.dmu1)) % 16 == 0) && ((size_t)H * W < (1ull << 31));
+  if ((size_t)H * W >= (1ull << 32)) return;  // in-plane offsets are 32-bit (api.cu rejects such sizes earlier)
+  if (vec) {
+    loss_pass1_kernel<true><<<grid, 256, 0, s>>>(p);
+    loss_pass2_kernel<true><<<grid, 256, 0, s>>>(p);
+  } else {
+    loss_pass1_kernel<false><<<grid, 256, 0, s>>>(p);
+    loss_pass2_kernel<false><<<grid, 256, 0, s>>>(p);
+  }
   size_t nblk = (size_t)grid.x * grid.y * grid.z;
   loss_final_kernel<<<1, 256, 0, s>>>(p.partial, nblk, 1.0 / (3.0 * (double)H * (double)W), (double)V * (1.0 - (double)lambda),
                                       loss_sum);

@@ -38,6 +38,20 @@ def test_fused_loss_matches_torch_at_image_size(cuda_dev, native):
     assert float((p2.grad - pred.grad / 7.0).abs().max()) <= 1e-3 * float(pred.grad.abs().max()) / 7.0
 
 
+@pytest.mark.parametrize("H,W", [(70, 93), (33, 40), (129, 258)])
+def test_fused_loss_odd_sizes_match_torch(cuda_dev, native, H, W):
+    """Widths that are not a multiple of 4 take the scalar staging path; ragged right/bottom tiles either way."""
+    from igs_b200 import refine
+    gen = torch.Generator().manual_seed(H * 1000 + W)
+    pred = torch.rand(2, 3, H, W, generator=gen).to(cuda_dev).requires_grad_(True)
+    gt = torch.rand(2, 3, H, W, generator=gen).to(cuda_dev)
+    ref = refine.refine_loss_torch(pred, gt, 0.8).sum()
+    ref.backward()
+    loss, dpred = native.refine_loss(pred.detach(), gt, 0.8, 0.5)
+    assert abs(float(loss) - float(ref)) <= 1e-5 * abs(float(ref))
+    assert float((dpred - 0.5 * pred.grad).abs().max()) <= 1e-3 * float(pred.grad.abs().max()) * 0.5
+
+
 def test_fused_adam_matches_torch_adam(cuda_dev, native):
     gen = torch.Generator().manual_seed(9)
     n = 100_003
