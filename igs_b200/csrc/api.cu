@@ -339,11 +339,13 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   // temp: gradient records + per-(view,Gaussian) partials
   size_t grec_bytes = ((size_t)(R ? R : 1) * ns * sizeof(float) + 255) & ~size_t(255);
   size_t part_bytes = VP * 16 * sizeof(float);
-  char* tmp = temp_alloc(temp_user, grec_bytes + part_bytes + 512);
+  size_t sums_bytes = VP * (ns == 16 ? 12 : 28) * sizeof(float);
+  char* tmp = temp_alloc(temp_user, grec_bytes + part_bytes + sums_bytes + 512);
   if (!tmp) { set_error("temp allocator returned NULL"); return IGS_ERR_ALLOC; }
   tmp = (char*)(((uintptr_t)tmp + 255) & ~uintptr_t(255));
   float* grec = (float*)tmp;
   float* partial = (float*)(tmp + grec_bytes);
+  float* sums = (float*)(tmp + grec_bytes + part_bytes);
 
   if (R > 0) {
     BlendBwdParams bp;
@@ -363,7 +365,7 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   gp.P = P; gp.V = V; gp.W = W; gp.H = H; gp.ns = ns; gp.focal_x = focal_x; gp.focal_y = focal_y;
   gp.tan_fovx = a->tan_fovx; gp.tan_fovy = a->tan_fovy; gp.kernel_size = a->kernel_size;
   gp.means3D = a->means3D; gp.cams = G.cams; gp.cov3D = G.cov3D; gp.eig = G.eig; gp.head = G.head; gp.radii = G.radii;
-  gp.tiles = G.tiles; gp.rank = G.rank; gp.sorted_gid = G.sval[(hv.flags >> 8) & 1]; gp.inst_off = G.inst_off; gp.clamped = G.clamped; gp.grec = grec;
+  gp.tiles = G.tiles; gp.rank = G.rank; gp.sorted_gid = G.sval[(hv.flags >> 8) & 1]; gp.inst_off = G.inst_off; gp.clamped = G.clamped; gp.grec = grec; gp.sums = sums;
   gp.dL_dmeans2D = a->dL_dmeans2D; gp.partial = partial;
   { StageScope st(IGS_STAGE_GATHER_BWD, s); launch_gather_bwd(gp, s); }
   if (int e = debug_sync(dbg, s, "gather backward")) return e;

@@ -78,6 +78,7 @@ struct GatherBwdParams {
   const uint32_t* inst_off;
   const uint8_t* clamped;
   const float* grec;
+  float* sums;         // [V*P][12 | 28] per-(view, Gaussian) sums of the records, by depth-sorted position
   float* dL_dmeans2D;  // [V*P][3]
   float* partial;      // [V*P][16]: dmean3, dcov6, dRGB3(clamp applied), dopacity, rawRGB3
 };

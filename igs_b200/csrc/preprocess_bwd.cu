@@ -26,7 +26,41 @@
 namespace igs {
 
 
-__global__ void __launch_bounds__(128)
+// Sum of each (view, Gaussian)'s gradient records.  Records of one Gaussian are consecutive (emission slots), and
+// positions are walked in depth-sorted order, so neighbouring threads read neighbouring memory: NS/4 lanes per
+// position, one 16-byte part each.  Kept apart from gather_bwd_kernel (146 registers, 16 % occupancy) so that this
+// bandwidth-bound half runs at full occupancy; the k-order of the additions is the list order (deterministic).
+template <int NS>
+__global__ void __launch_bounds__(256)
+sum_records_kernel(size_t VP, const uint32_t* __restrict__ inst_off, const float* __restrict__ grec,
+                   float* __restrict__ sums) {
+  constexpr int LANES = NS / 4;                // 16-byte parts per record
+  constexpr int PARTS = NS == 16 ? 3 : 7;      // parts that carry values (10 / 25 floats)
+  const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t pos = t / LANES;
+  const int part = (int)(t % LANES);
+  if (pos >= VP || part >= PARTS) return;
+  const uint32_t off = inst_off[pos];
+  const uint32_t n = inst_off[pos + 1] - off;
+  const float4* r = reinterpret_cast<const float4*>(grec) + (size_t)off * LANES + part;
+  float4 acc = make_float4(0, 0, 0, 0);
+  uint32_t k = 0;
+  for (; k + 4 <= n; k += 4) {
+    const float4 a = r[(size_t)k * LANES], b = r[(size_t)(k + 1) * LANES], c = r[(size_t)(k + 2) * LANES],
+                 d = r[(size_t)(k + 3) * LANES];
+    acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+    acc.x += b.x; acc.y += b.y; acc.z += b.z; acc.w += b.w;
+    acc.x += c.x; acc.y += c.y; acc.z += c.z; acc.w += c.w;
+    acc.x += d.x; acc.y += d.y; acc.z += d.z; acc.w += d.w;
+  }
+  for (; k < n; k++) {
+    const float4 a = r[(size_t)k * LANES];
+    acc.x += a.x; acc.y += a.y; acc.z += a.z; acc.w += a.w;
+  }
+  reinterpret_cast<float4*>(sums)[pos * PARTS + part] = acc;
+}
+
+__global__ void __launch_bounds__(128, 4)
 gather_bwd_kernel(GatherBwdParams p) {
   // Threads are indexed by DEPTH-SORTED position: emission slots of neighbouring positions are adjacent in grec, so
   // the record reads of a warp fall into one contiguous region (the small per-Gaussian inputs become the gathers).
@@ -42,44 +76,22 @@ gather_bwd_kernel(GatherBwdParams p) {
     dm2[0] = dm2[1] = dm2[2] = 0.0f;
     return;
   }
-  // ---- sum the instance records ----
+  // ---- the instance records of this (view, Gaussian), already summed by sum_records_kernel ----
   float s[25];
 #pragma unroll
   for (int i = 0; i < 25; i++) s[i] = 0.0f;
-  {
-    const uint32_t off = p.inst_off[pos];
-    const uint32_t n = p.inst_off[pos + 1] - off;
-    if (p.ns == 16) {
-      const float4* r = reinterpret_cast<const float4*>(p.grec + (size_t)off * 16);
-      uint32_t k = 0;
-      for (; k + 4 <= n; k += 4) {  // 12 independent 16-byte loads in flight per thread (the kernel is latency bound)
-        float4 a[4], b[4], c[4];
+  if (p.ns == 16) {
+    const float4* r = reinterpret_cast<const float4*>(p.sums) + pos * 3;
+    const float4 a = r[0], b = r[1], c = r[2];
+    s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w; s[8] = c.x; s[9] = c.y;
+  } else {
+    const float4* r = reinterpret_cast<const float4*>(p.sums) + pos * 7;
 #pragma unroll
-        for (int u = 0; u < 4; u++) { a[u] = r[(k + u) * 4 + 0]; b[u] = r[(k + u) * 4 + 1]; c[u] = r[(k + u) * 4 + 2]; }
-#pragma unroll
-        for (int u = 0; u < 4; u++) {
-          s[0] += a[u].x; s[1] += a[u].y; s[2] += a[u].z; s[3] += a[u].w;
-          s[4] += b[u].x; s[5] += b[u].y; s[6] += b[u].z; s[7] += b[u].w;
-          s[8] += c[u].x; s[9] += c[u].y;
-        }
-      }
-      for (; k < n; k++) {
-        float4 a = r[k * 4 + 0], b = r[k * 4 + 1], c = r[k * 4 + 2];
-        s[0] += a.x; s[1] += a.y; s[2] += a.z; s[3] += a.w;
-        s[4] += b.x; s[5] += b.y; s[6] += b.z; s[7] += b.w;
-        s[8] += c.x; s[9] += c.y;
-      }
-    } else {
-      const float4* r = reinterpret_cast<const float4*>(p.grec + (size_t)off * 32);
-      for (uint32_t k = 0; k < n; k++) {
-#pragma unroll
-        for (int q = 0; q < 6; q++) {
-          float4 a = r[k * 8 + q];
-          s[q * 4 + 0] += a.x; s[q * 4 + 1] += a.y; s[q * 4 + 2] += a.z; s[q * 4 + 3] += a.w;
-        }
-        s[24] += r[k * 8 + 6].x;
-      }
+    for (int q = 0; q < 6; q++) {
+      const float4 a = r[q];
+      s[q * 4 + 0] = a.x; s[q * 4 + 1] = a.y; s[q * 4 + 2] = a.z; s[q * 4 + 3] = a.w;
     }
+    s[24] = r[6].x;
   }
   const float dL_dopacity_in = s[9];
   dm2[0] = s[3]; dm2[1] = s[4]; dm2[2] = s[5];
@@ -501,7 +513,9 @@ finish_bwd_kernel(FinishBwdParams p) {
 void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s) {
   if (p.P <= 0) return;
   const size_t VP = (size_t)p.V * p.P;
-  count_launch();
+  count_launch(2);
+  if (p.ns == 16) sum_records_kernel<16><<<(unsigned)((VP * 4 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums);
+  else sum_records_kernel<32><<<(unsigned)((VP * 8 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums);
   gather_bwd_kernel<<<(unsigned)((VP + 127) / 128), 128, 0, s>>>(p);
 }
 
