@@ -61,8 +61,12 @@ FwdRet forward_impl(const torch::Tensor& background, const torch::Tensor& means3
   auto fopt = means3D.options().dtype(torch::kFloat32);
   auto iopt = means3D.options().dtype(torch::kInt32);
   auto shape = [&](int C) { return batched ? std::vector<int64_t>{V, C, H, W} : std::vector<int64_t>{C, H, W}; };
-  // one zero-filled slab for the 15 output planes (the reference zero-fills 8 tensors separately)
-  torch::Tensor slab = torch::zeros({(int64_t)V * 15, H, W}, fopt);
+  // One slab for the 15 output planes (the reference zero-fills 8 tensors separately).  With require_coord and
+  // require_depth the blend kernel writes every pixel of every plane, so the slab needs no memset (1.6 GB at C3);
+  // otherwise the planes that are not produced must read as zeros, like the reference's.
+  const bool all_planes_written = require_coord && require_depth && P != 0;
+  torch::Tensor slab = all_planes_written ? torch::empty({(int64_t)V * 15, H, W}, fopt)
+                                          : torch::zeros({(int64_t)V * 15, H, W}, fopt);
   int64_t plane = (int64_t)H * W;
   auto view_of = [&](int64_t first, int C) {
     return slab.narrow(0, first, (int64_t)V * C).view(shape(C));
