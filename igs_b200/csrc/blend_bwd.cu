@@ -58,6 +58,7 @@ __global__ void __launch_bounds__(256, MINB)
 blend_bwd_kernel(BlendBwdParams p) {
   constexpr int NS = GEOGRAD ? 32 : 16;         // floats per gradient record in global memory
   constexpr int NV = GEOGRAD ? 25 : 10;         // values actually produced per pair
+  constexpr int AS = GEOGRAD ? 25 : 11;         // accumulator stride per batch slot (colour-only: + one sink word)
   constexpr int BATCH = bwd_batch(GEOGRAD, MINB);
   constexpr bool GEO = GEOGRAD && (COORD || DEPTH || NORMAL);
   // survivors: [0,B) head.a {x, y, conic.x, conic.y}; [B,2B) head.b {conic.z, opacity, r, g};
@@ -74,7 +75,6 @@ blend_bwd_kernel(BlendBwdParams p) {
   extern __shared__ float s_acc[];
   // colour-only path: per-warp [10][36] transpose staging for the cross-pixel reduction (columns 32..35 stay zero)
   __shared__ __align__(16) float s_stage[GEOGRAD ? 4 : 8 * 10 * 36];
-  __shared__ float s_dummy[GEOGRAD ? 1 : 256];  // sink for the lanes that own no value in the reduction
 
   const int tiles = p.tiles_x * p.tiles_y;
   const int gt = blockIdx.x;
@@ -97,8 +97,8 @@ blend_bwd_kernel(BlendBwdParams p) {
   const float bx1 = (float)min(wx0 + 7, p.W - 1), by1 = (float)min(wy0 + 3, p.H - 1);
   const uint32_t rec_base = smem_addr(s_rec);
   const uint32_t tail_base = smem_addr(s_t);
-  const uint32_t acc_base = smem_addr(s_acc) + (uint32_t)w * (BATCH * NV * 4);
-  for (uint32_t f = threadIdx.x; f < 8 * BATCH * NV; f += 256) s_acc[f] = 0.0f;
+  const uint32_t acc_base = smem_addr(s_acc) + (uint32_t)w * (BATCH * AS * 4);
+  for (uint32_t f = threadIdx.x; f < 8 * BATCH * AS; f += 256) s_acc[f] = 0.0f;
   if constexpr (!GEOGRAD) {
     for (uint32_t f = threadIdx.x; f < 8 * 10 * 36; f += 256) s_stage[f] = 0.0f;
   }
@@ -108,9 +108,9 @@ blend_bwd_kernel(BlendBwdParams p) {
   const uint32_t stage_wr = stage_base + (uint32_t)lane * 4;
   const bool red_owner = (rs == 0u) && (lane < 30);
   const uint32_t stage_rd = stage_base + (lane < 30 ? (rv * 36 + rs * 12) * 4 : 0u);  // lanes 30, 31: any valid row
-  // accumulator address of this lane for batch slot s is red_base + s * red_mul (non-owners hit their dummy word)
-  const uint32_t red_base = red_owner ? acc_base + rv * 4 : smem_addr(s_dummy) + threadIdx.x * 4;
-  const uint32_t red_mul = red_owner ? (uint32_t)(NV * 4) : 0u;
+  // accumulator address of this lane for batch slot s is red_base + s * AS * 4: the 10 owner lanes hit the slot's 10
+  // values, every other lane the slot's 11th word (one broadcast address in the bank next to the owners': no conflicts)
+  const uint32_t red_base = acc_base + (red_owner ? rv : 10u) * 4;
 
   const uint2 range = p.ranges[gt];
   const uint32_t last_contributor = inside ? p.n_contrib[(size_t)v * 2 * N + pix_id] : 0u;
@@ -363,7 +363,7 @@ blend_bwd_kernel(BlendBwdParams p) {
         if constexpr (GEOGRAD) {
           warp_reduce_scatter<NS>(val, lane);  // afterwards lane L holds the warp sum of value L
           if (lane < NV) {
-            const uint32_t aa = acc_base + (__float_as_uint(cq.w) * NV + lane) * 4;
+            const uint32_t aa = acc_base + (__float_as_uint(cq.w) * AS + lane) * 4;
             sts32<0>(aa, lds32<0>(aa) + val[0]);
           }
         } else {
@@ -378,7 +378,7 @@ blend_bwd_kernel(BlendBwdParams p) {
           float sum = hsum2(add2(add2(add2(pack2(x0.x, x0.y), pack2(x0.z, x0.w)), add2(pack2(x1.x, x1.y), pack2(x1.z, x1.w))),
                                  add2(pack2(x2.x, x2.y), pack2(x2.z, x2.w))));
           sum += __shfl_down_sync(0xffffffffu, sum, 1) + __shfl_down_sync(0xffffffffu, sum, 2);
-          const uint32_t aa = red_base + __float_as_uint(cq.w) * red_mul;
+          const uint32_t aa = red_base + __float_as_uint(cq.w) * (uint32_t)(AS * 4);
           sts32<0>(aa, lds32<0>(aa) + sum);
           __syncwarp();
         }
@@ -392,7 +392,7 @@ blend_bwd_kernel(BlendBwdParams p) {
       if (q < NV) {
 #pragma unroll
         for (int ww = 0; ww < 8; ww++) {
-          float* pa = s_acc + ((size_t)ww * BATCH + sl) * NV + q;
+          float* pa = s_acc + ((size_t)ww * BATCH + sl) * AS + q;
           sum += *pa;
           *pa = 0.0f;
         }
@@ -408,7 +408,7 @@ int blend_bwd_record_floats(bool geograd) { return geograd ? 32 : 16; }
 
 template <bool C, bool D, bool N, bool G, int MINB>
 static void launch_one(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
-  constexpr int bytes = 8 * bwd_batch(G, MINB) * (G ? 25 : 10) * 4;  // per-warp accumulators (dynamic shared memory)
+  constexpr int bytes = 8 * bwd_batch(G, MINB) * (G ? 25 : 11) * 4;  // per-warp accumulators (dynamic shared memory)
   // > 48 KB of dynamic shared memory needs the opt-in; it is per device, so it is (cheaply) set on every launch
   cudaFuncSetAttribute(blend_bwd_kernel<C, D, N, G, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
   blend_bwd_kernel<C, D, N, G, MINB><<<nblocks, 256, bytes, s>>>(p);
