@@ -146,9 +146,26 @@ def case_empty_view():
     return c
 
 
+def case_kernel3d():
+    """kernel_size != 0 (RaDe-GS frame-0 training uses 0.1): the low-pass term of computeCov2D and the opacity
+    compensation coef = sqrt(det_0 / det_1), forward and backward (SURVEY T5 / T19 with kernel_size != 0)."""
+    c = _base(1200, 96, 80, 90, math.log(0.2), view=1)
+    c["kernel_size"] = 0.1
+    return c
+
+
+def case_scalemod():
+    """scale_modifier != 1 together with a large kernel_size."""
+    c = _base(900, 80, 64, 100, math.log(0.3), view=2)
+    c["kernel_size"] = 0.3
+    c["scale_modifier"] = 0.7
+    return c
+
+
 CASES = {
     "small": case_small, "dense": case_dense, "edge": case_edge, "precomp": case_precomp, "sh1": case_sh1,
     "sh0_nogeo": case_sh0_nogeo, "depthonly": case_depthonly, "empty_view": case_empty_view,
+    "kernel3d": case_kernel3d, "scalemod": case_scalemod,
 }
 
 
