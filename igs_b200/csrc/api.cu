@@ -506,4 +506,32 @@ int igs_activate_backward(int P, const float* scales, const float* raw_rot, cons
   return IGS_OK;
 }
 
+int igs_densify_stats(int P, int V, const float* dL_dmeans2D, const int* radii, float* grad_accum, float* denom,
+                      float* max_radii2D, void* stream) {
+  if (P < 0 || V < 0) { set_error("bad argument"); return IGS_ERR_INVALID; }
+  if (P == 0 || V == 0) return IGS_OK;
+  if (!dL_dmeans2D || !radii || !grad_accum || !denom || !max_radii2D) { set_error("null pointer"); return IGS_ERR_INVALID; }
+  launch_densify_stats(P, V, dL_dmeans2D, radii, grad_accum, denom, max_radii2D, (cudaStream_t)stream);
+  IGS_CUDA_CHECK(cudaGetLastError());
+  return IGS_OK;
+}
+
+int igs_densify_gather(int P_old, int P_new, const int* src, const unsigned char* kind, const float* samples,
+                       float split_div, const size_t* off_old, const size_t* off_new, const float* param_old,
+                       const float* exp_avg_old, const float* exp_avg_sq_old, float* param_new, float* exp_avg_new,
+                       float* exp_avg_sq_new, void* stream) {
+  if (P_old < 0 || P_new < 0) { set_error("bad argument"); return IGS_ERR_INVALID; }
+  if (P_new == 0) return IGS_OK;
+  if (!src || !kind || !off_old || !off_new || !param_old || !exp_avg_old || !exp_avg_sq_old || !param_new ||
+      !exp_avg_new || !exp_avg_sq_new) {
+    set_error("null pointer");
+    return IGS_ERR_INVALID;
+  }
+  if (!(split_div > 0.0f)) { set_error("split_div must be positive"); return IGS_ERR_INVALID; }
+  launch_densify_gather(P_old, P_new, src, kind, samples, split_div, off_old, off_new, param_old, exp_avg_old,
+                        exp_avg_sq_old, param_new, exp_avg_new, exp_avg_sq_new, (cudaStream_t)stream);
+  IGS_CUDA_CHECK(cudaGetLastError());
+  return IGS_OK;
+}
+
 }  // extern "C"

@@ -134,6 +134,12 @@ void launch_activate_fwd(int P, const float* log_scales, const float* raw_rot, c
 void launch_activate_bwd(int P, const float* scales, const float* raw_rot, const float* opac, const float* dL_dscales,
                          const float* dL_drot, const float* dL_dopac, float* dL_dlog_scales, float* dL_draw_rot,
                          float* dL_dlogit, cudaStream_t s);
+void launch_densify_stats(int P, int V, const float* g2d, const int* radii, float* grad_accum, float* denom,
+                          float* max_radii, cudaStream_t s);
+void launch_densify_gather(int P_old, int P_new, const int* src, const uint8_t* kind, const float* samples,
+                           float split_div, const size_t* off_old, const size_t* off_new, const float* param_old,
+                           const float* m_old, const float* v_old, float* param_new, float* m_new, float* v_new,
+                           cudaStream_t s);
 void launch_adam_groups(float* p, const float* g, float* m, float* v, int ngroups, const size_t* sizes,
                         const float* step_sizes, float b1, float b2, float eps, float inv_sqrt_bc2, cudaStream_t s);
 

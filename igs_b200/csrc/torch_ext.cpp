@@ -465,6 +465,52 @@ std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor> RefineGrad(
   return std::make_tuple(loss, (int64_t)rendered, std::get<8>(f), std::get<0>(b));
 }
 
+void DensifyStats(const torch::Tensor& g2d, const torch::Tensor& radii, torch::Tensor& grad_accum, torch::Tensor& denom,
+                  torch::Tensor& max_radii) {
+  TORCH_CHECK(g2d.is_cuda() && radii.is_cuda() && grad_accum.is_cuda(), "densify_stats needs CUDA tensors (there is no CPU path)");
+  TORCH_CHECK(g2d.dim() == 3 && g2d.size(2) == 3 && radii.dim() == 2, "dL_dmeans2D must be [V,P,3] and radii [V,P]");
+  TORCH_CHECK(radii.scalar_type() == torch::kInt32, "radii must be int32");
+  const int V = (int)g2d.size(0), P = (int)g2d.size(1);
+  TORCH_CHECK(radii.size(0) == V && radii.size(1) == P && grad_accum.numel() == P && denom.numel() == P && max_radii.numel() == P,
+              "size mismatch");
+  TORCH_CHECK(grad_accum.is_contiguous() && denom.is_contiguous() && max_radii.is_contiguous(), "statistics must be contiguous");
+  const c10::cuda::CUDAGuard guard(g2d.device());
+  torch::Tensor g = g2d.contiguous(), r = radii.contiguous();
+  check(igs_densify_stats(P, V, fptr(g, "dL_dmeans2D"), r.data_ptr<int>(), grad_accum.data_ptr<float>(),
+                          denom.data_ptr<float>(), max_radii.data_ptr<float>(),
+                          (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "densify_stats");
+}
+
+// (param_new, exp_avg_new, exp_avg_sq_new) = packed records of P_new Gaussians gathered from the old ones
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> DensifyGather(
+    const torch::Tensor& param, const torch::Tensor& exp_avg, const torch::Tensor& exp_avg_sq, int64_t P_old,
+    const torch::Tensor& src, const torch::Tensor& kind, const torch::Tensor& samples, double split_div,
+    const std::vector<int64_t>& off_old, const std::vector<int64_t>& off_new) {
+  TORCH_CHECK(param.is_cuda() && exp_avg.is_cuda() && exp_avg_sq.is_cuda() && src.is_cuda() && kind.is_cuda(),
+              "densify_gather needs CUDA tensors (there is no CPU path)");
+  TORCH_CHECK(src.scalar_type() == torch::kInt32 && kind.scalar_type() == torch::kUInt8, "src int32, kind uint8");
+  TORCH_CHECK(off_old.size() == 5 && off_new.size() == 5, "offsets of (xyz, rotation, shs, opacity, scaling)");
+  TORCH_CHECK(param.numel() == P_old * 59 && exp_avg.numel() == P_old * 59 && exp_avg_sq.numel() == P_old * 59,
+              "old records must hold P_old * 59 floats");
+  const int64_t P_new = src.numel();
+  TORCH_CHECK(kind.numel() == P_new, "kind / src size mismatch");
+  const c10::cuda::CUDAGuard guard(param.device());
+  torch::Tensor pn = torch::empty({P_new * 59}, param.options()), mn = torch::empty({P_new * 59}, param.options()),
+                vn = torch::empty({P_new * 59}, param.options());
+  torch::Tensor sc = src.contiguous(), kc = kind.contiguous(), sm = samples.defined() ? samples.contiguous() : samples;
+  if (sm.defined() && sm.numel() != 0) TORCH_CHECK(sm.numel() == P_new * 3 && sm.is_cuda(), "samples must be [P_new,3] on the device");
+  size_t oo[5], on[5];
+  for (int k = 0; k < 5; k++) { oo[k] = (size_t)off_old[k]; on[k] = (size_t)off_new[k]; }
+  torch::Tensor po = param.contiguous(), mo = exp_avg.contiguous(), vo = exp_avg_sq.contiguous();
+  check(igs_densify_gather((int)P_old, (int)P_new, sc.data_ptr<int>(), kc.data_ptr<uint8_t>(), fptr(sm, "samples"),
+                           (float)split_div, oo, on, po.data_ptr<float>(), mo.data_ptr<float>(), vo.data_ptr<float>(),
+                           pn.data_ptr<float>(), mn.data_ptr<float>(), vn.data_ptr<float>(),
+                           (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "densify_gather");
+  return std::make_tuple(pn, mn, vn);
+}
+
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("refine_loss", &RefineLoss, pybind11::arg("pred"), pybind11::arg("gt"), pybind11::arg("lambda_l1"),
         pybind11::arg("grad_scale") = 1.0);
@@ -472,6 +518,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("activate_forward", &ActivateForward);
   m.def("activate_backward", &ActivateBackward);
   m.def("adam_step_groups", &AdamStepGroups);
+  m.def("densify_stats", &DensifyStats);
+  m.def("densify_gather", &DensifyGather);
   m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
   m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
   m.def("mark_visible", &markVisible);

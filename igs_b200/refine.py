@@ -54,6 +54,19 @@ class RefineState:
             off += P * k
         self.step = 0
 
+    def resize(self, P: int, flat: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor) -> None:
+        """Adopts re-laid-out records of a new size (densify / prune, igs_b200/densify.py); Adam's step count is kept,
+        like the reference, which keeps `state["step"]` of every surviving parameter group."""
+        n = P * FLOATS_PER_GAUSSIAN
+        assert flat.numel() == n and exp_avg.numel() == n and exp_avg_sq.numel() == n
+        self.P = P
+        self.flat, self.exp_avg, self.exp_avg_sq = flat, exp_avg, exp_avg_sq
+        self.grad = torch.zeros(n, device=self.device, dtype=torch.float32)
+        off = 0
+        for name, k in GROUPS:
+            self.slices[name] = (off, off + P * k, k)
+            off += P * k
+
     def view(self, buf: torch.Tensor, name: str) -> torch.Tensor:
         a, b, k = self.slices[name]
         t = buf[a:b]

@@ -21,6 +21,8 @@
  *                              (igs/models/gaussian_model.py:348; infer_batch.py:323)
  *   igs_refine_loss         <- 0.8*L1 + 0.2*(1-SSIM) (infer_batch.py:301-305, igs/utils/loss_utils.py:16-62)
  *   igs_activate_forward/backward <- exp / normalize / sigmoid activations (igs/models/gaussian_model.py:89-127)
+ *   igs_densify_stats / igs_densify_gather <- densification statistics and the parameter / optimizer-state rebuild
+ *                              of densify_and_prune (igs/models/gaussian_model.py:466-666,865-868)
  *
  * Conventions
  *   - All pointers are DEVICE pointers unless stated otherwise; float = IEEE fp32; layouts are the
@@ -55,7 +57,7 @@
 extern "C" {
 #endif
 
-#define IGS_RASTER_ABI_VERSION 2
+#define IGS_RASTER_ABI_VERSION 3
 
 typedef enum igs_status {
   IGS_OK = 0,
@@ -226,6 +228,28 @@ int igs_activate_forward(int P, const float* log_scales, const float* raw_rot, c
 int igs_activate_backward(int P, const float* scales, const float* raw_rot, const float* opacities,
                           const float* dL_dscales, const float* dL_drot, const float* dL_dopac,
                           float* dL_dlog_scales, float* dL_draw_rot, float* dL_dlogit, void* stream);
+
+/* Densification statistics of one step, all V views at once (igs/models/gaussian_model.py:865-868
+ * `add_densification_stats` and the max_radii2D update of infer_batch.py:312-313, which the reference runs once per
+ * single-view iteration):  for every view v with radii[v][g] > 0:  grad_accum[g] += |dL_dmeans2D[v][g].xy|,
+ * denom[g] += 1, max_radii2D[g] = max(max_radii2D[g], radii[v][g]).  dL_dmeans2D is [V][P][3], radii [V][P]. */
+int igs_densify_stats(int P, int V, const float* dL_dmeans2D, const int* radii, float* grad_accum, float* denom,
+                      float* max_radii2D, void* stream);
+
+/* Re-layout of the packed parameter record and both Adam moments after densify / prune, in one pass (replaces the
+ * torch.cat / boolean-index rebuild of every nn.Parameter and optimizer state in igs/models/gaussian_model.py:466-557,
+ * three times per densify_and_prune call).  New Gaussian i takes the record of old Gaussian src[i]:
+ *   kind[i] == 0  keep:  parameters and moments carried over
+ *   kind[i] == 1  clone: parameters copied, moments zero                       (densify_and_clone, :619-638)
+ *   kind[i] == 2  split child: parameters copied, moments zero,
+ *                 xyz = build_rotation(rotation) * samples[i] + xyz,  log_scale = log(exp(log_scale) / split_div)
+ *                                                                               (densify_and_split, :586-615)
+ * off_old / off_new (HOST arrays of 5) are the element offsets of (xyz, rotation, shs[48], opacity, scaling) inside
+ * the old / new records; the old and new arrays must not overlap. */
+int igs_densify_gather(int P_old, int P_new, const int* src, const unsigned char* kind, const float* samples,
+                       float split_div, const size_t* off_old, const size_t* off_new, const float* param_old,
+                       const float* exp_avg_old, const float* exp_avg_sq_old, float* param_new, float* exp_avg_new,
+                       float* exp_avg_sq_new, void* stream);
 
 const char* igs_last_error(void);
 int igs_abi_version(void);
