@@ -38,6 +38,16 @@ class DensifyStats:
         from . import _C
         _C.densify_stats(grad_means2D, radii, self.grad_accum, self.denom, self.max_radii2D)
 
+    def all_reduce(self, group=None) -> None:
+        """View-sharded refine: every rank saw only its views.  SUM the accumulators and MAX the radii over the
+        ranks, so that every rank plans the identical densification (same statistics, same parameters, same seeded
+        generator) and no broadcast of the new parameters is needed."""
+        if group is None or torch.distributed.get_world_size(group) <= 1:
+            return
+        torch.distributed.all_reduce(self.grad_accum, group=group)
+        torch.distributed.all_reduce(self.denom, group=group)
+        torch.distributed.all_reduce(self.max_radii2D, op=torch.distributed.ReduceOp.MAX, group=group)
+
     def update_torch(self, grad_means2D: torch.Tensor, radii: torch.Tensor) -> None:
         """The same update with torch ops (restatement used by the tests)."""
         for v in range(radii.shape[0]):
