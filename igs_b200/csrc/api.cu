@@ -71,14 +71,23 @@ StageScope::~StageScope() {
 
 // ---- small kernels local to this file ----
 __global__ void pack_cameras_kernel(int V, const float* __restrict__ view, const float* __restrict__ proj,
-                                    const float* __restrict__ campos, Camera* __restrict__ cams) {
+                                    const float* __restrict__ campos, const int* __restrict__ tile_rows, int tiles_y,
+                                    Camera* __restrict__ cams) {
   int v = blockIdx.x;
   int t = threadIdx.x;
   if (v >= V) return;
   if (t < 16) cams[v].view[t] = view[v * 16 + t];
   else if (t < 32) cams[v].proj[t - 16] = proj[v * 16 + (t - 16)];
   else if (t < 35) cams[v].campos[t - 32] = campos[v * 3 + (t - 32)];
-  else if (t == 35) cams[v].pad = 0.0f;
+  else if (t == 35) {
+    int r0 = 0, r1 = tiles_y;
+    if (tile_rows != nullptr) {
+      r0 = min(tiles_y, max(0, tile_rows[2 * v]));
+      r1 = min(tiles_y, max(r0, tile_rows[2 * v + 1]));
+    }
+    cams[v].row0 = r0;
+    cams[v].row1 = r1;
+  }
 }
 
 __global__ void write_header_kernel(Header* h, Header v, const uint32_t* total) {
@@ -130,8 +139,10 @@ extern "C" {
 const char* igs_last_error(void) { return igs::g_err; }
 int igs_abi_version(void) { return IGS_RASTER_ABI_VERSION; }
 int igs_refine_loss(const float* pred, const float* gt, int V, int height, int width, float lambda_l1, float grad_scale,
-                    float* loss_sum, float* dL_dpred, igs_alloc_fn temp_alloc, void* temp_user, void* stream) {
+                    const int* loss_rows, float* loss_sum, float* dL_dpred, igs_alloc_fn temp_alloc, void* temp_user,
+                    void* stream) {
   if (V < 0 || height <= 0 || width <= 0 || !temp_alloc) { set_error("bad argument"); return IGS_ERR_INVALID; }
+  if (loss_rows && V > 64) { set_error("loss_rows supports at most 64 views per call"); return IGS_ERR_UNSUPPORTED; }
   if (V == 0) return IGS_OK;
   if (!pred || !gt || !loss_sum || !dL_dpred) { set_error("null pointer"); return IGS_ERR_INVALID; }
   size_t bytes = refine_loss_scratch_bytes(V, height, width);
@@ -140,7 +151,8 @@ int igs_refine_loss(const float* pred, const float* gt, int V, int height, int w
   tmp = (char*)(((uintptr_t)tmp + 255) & ~uintptr_t(255));
   {
     StageScope st(IGS_STAGE_LOSS, (cudaStream_t)stream);
-    launch_refine_loss(pred, gt, V, height, width, lambda_l1, grad_scale, loss_sum, dL_dpred, tmp, (cudaStream_t)stream);
+    launch_refine_loss(pred, gt, V, height, width, lambda_l1, grad_scale, loss_rows, loss_sum, dL_dpred, tmp,
+                       (cudaStream_t)stream);
   }
   IGS_CUDA_CHECK(cudaGetLastError());
   return IGS_OK;
@@ -200,7 +212,7 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   write_tag_kernel<<<1, 1, 0, s>>>(I.tag, BufTag{IGS_TAG_IMG, 0u, (uint32_t)V, (uint32_t)N});
 
   count_launch();
-  pack_cameras_kernel<<<V, 64, 0, s>>>(V, a->viewmatrix, a->projmatrix, a->cam_pos, G.cams);
+  pack_cameras_kernel<<<V, 64, 0, s>>>(V, a->viewmatrix, a->projmatrix, a->cam_pos, a->tile_rows, tiles_y, G.cams);
   { StageScope st(IGS_STAGE_GAUSS_SETUP, s);
   launch_gauss_setup(P, a->scales, a->scale_modifier, a->rotations, a->cov3D_precomp, G.cov3D, G.eig, s); }
   if (int e = debug_sync(dbg, s, "gauss_setup")) return e;
@@ -249,7 +261,7 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   int bcur = 0;
   if (R > 0) {
     { StageScope st(IGS_STAGE_EMIT, s);
-      launch_emit_instances(VP, (uint32_t)P, tiles_x, tiles_y, sorted_gid, G.inst_off, G.head, G.radii, B.tkey[0],
+      launch_emit_instances(VP, (uint32_t)P, tiles_x, tiles_y, G.cams, sorted_gid, G.inst_off, G.head, G.radii, B.tkey[0],
                             B.tval[0], B.inst_gid, s); }
     if (int e = debug_sync(dbg, s, "emit")) return e;
     { StageScope st(IGS_STAGE_TILE_SORT, s);

@@ -258,17 +258,18 @@ void launch_gather_rank(size_t VP, const uint32_t* sorted_gid, const uint32_t* t
 // Instance emission (reference duplicateWithKeys, rasterizer_impl.cu:70-111, getRect auxiliary.h:62-72)
 // One thread per depth-sorted Gaussian; emission slot e = inst_off[i] + row-major tile index.
 // ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void tile_rect(float px, float py, int radius, int tiles_x, int tiles_y, int& x0, int& y0,
-                                          int& x1, int& y1) {
+__device__ __forceinline__ void tile_rect(float px, float py, int radius, int tiles_x, int row0, int row1, int& x0,
+                                          int& y0, int& x1, int& y1) {
   float rf = (float)radius;
   x0 = min(tiles_x, max(0, (int)fmul(fsub(px, rf), 0.0625f)));
-  y0 = min(tiles_y, max(0, (int)fmul(fsub(py, rf), 0.0625f)));
+  y0 = min(row1, max(row0, (int)fmul(fsub(py, rf), 0.0625f)));
   x1 = min(tiles_x, max(0, (int)fmul(fadd(fadd(fadd(px, rf), 16.0f), -1.0f), 0.0625f)));
-  y1 = min(tiles_y, max(0, (int)fmul(fadd(fadd(fadd(py, rf), 16.0f), -1.0f), 0.0625f)));
+  y1 = min(row1, max(row0, (int)fmul(fadd(fadd(fadd(py, rf), 16.0f), -1.0f), 0.0625f)));
 }
 
 __global__ void __launch_bounds__(256)
-emit_instances_kernel(size_t VP, uint32_t P, int tiles_x, int tiles_y, const uint32_t* __restrict__ sorted_gid,
+emit_instances_kernel(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Camera* __restrict__ cams,
+                      const uint32_t* __restrict__ sorted_gid,
                       const uint32_t* __restrict__ inst_off, const SplatHead* __restrict__ head,
                       const int* __restrict__ radii, uint32_t* __restrict__ tkey, uint32_t* __restrict__ tval,
                       uint32_t* __restrict__ inst_gid) {
@@ -281,7 +282,7 @@ emit_instances_kernel(size_t VP, uint32_t P, int tiles_x, int tiles_y, const uin
   uint32_t v = gid / P;
   float4 h = head[gid].a;
   int x0, y0, x1, y1;
-  tile_rect(h.x, h.y, radii[gid], tiles_x, tiles_y, x0, y0, x1, y1);
+  tile_rect(h.x, h.y, radii[gid], tiles_x, cams[v].row0, cams[v].row1, x0, y0, x1, y1);
   uint32_t tbase = v * (uint32_t)(tiles_x * tiles_y);
   for (int y = y0; y < y1; y++)
     for (int x = x0; x < x1; x++) {
@@ -292,13 +293,14 @@ emit_instances_kernel(size_t VP, uint32_t P, int tiles_x, int tiles_y, const uin
     }
 }
 
-void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, const uint32_t* sorted_gid,
+void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Camera* cams,
+                           const uint32_t* sorted_gid,
                            const uint32_t* inst_off, const SplatHead* head, const int* radii, uint32_t* tkey,
                            uint32_t* tval, uint32_t* inst_gid, cudaStream_t s) {
   if (VP == 0) return;
   unsigned nb = (unsigned)((VP + 255) / 256);
   count_launch();
-  emit_instances_kernel<<<nb, 256, 0, s>>>(VP, P, tiles_x, tiles_y, sorted_gid, inst_off, head, radii, tkey, tval,
+  emit_instances_kernel<<<nb, 256, 0, s>>>(VP, P, tiles_x, tiles_y, cams, sorted_gid, inst_off, head, radii, tkey, tval,
                                            inst_gid);
 }
 

@@ -44,7 +44,7 @@ struct Camera {
   float view[16];
   float proj[16];
   float campos[3];
-  float pad;
+  int row0, row1;  // tile-row window [row0, row1) rendered for this view (whole image: 0, tiles_y)
 };
 
 struct Header {

@@ -114,7 +114,8 @@ int radix_sort_pairs(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint3
                      cudaStream_t s);
 void launch_gather_rank(size_t VP, const uint32_t* sorted_gid, const uint32_t* tiles, uint32_t* tiles_sorted,
                         uint32_t* rank, cudaStream_t s);
-void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, const uint32_t* sorted_gid,
+void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Camera* cams,
+                           const uint32_t* sorted_gid,
                            const uint32_t* inst_off, const SplatHead* head, const int* radii, uint32_t* tkey,
                            uint32_t* tval, uint32_t* inst_gid, cudaStream_t s);
 void launch_finalize_bins(uint32_t R, const uint32_t* tkey, const uint32_t* point_e, const uint32_t* inst_gid,
@@ -127,7 +128,7 @@ void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bo
 void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s);
 void launch_finish_bwd(const FinishBwdParams& p, cudaStream_t s);
 size_t refine_loss_scratch_bytes(int V, int H, int W);
-void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float grad_scale, float* loss_sum,
+void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float grad_scale, const int* loss_rows_host, float* loss_sum,
                         float* dpred, char* scratch, cudaStream_t s);
 void launch_activate_fwd(int P, const float* log_scales, const float* raw_rot, const float* logit, float* scales,
                          float* rot, float* opac, cudaStream_t s);

@@ -16,6 +16,7 @@
 
 namespace igs {
 
+#define IGS_LOSS_MAX_ROW_VIEWS 64
 #define LOSS_BX 32
 #define LOSS_BY 32
 #define LOSS_R 5
@@ -36,7 +37,16 @@ struct LossParams {
   float* dE12;
   float* dpred;
   double* partial;         // [gridDim.x*gridDim.y*gridDim.z]
+  // Optional per-view pixel-row ranges: the loss of view v is summed over rows [rows[2v], rows[2v+1]) only (a rank
+  // that renders a band of a view owns the loss terms of that band's rows).  has_rows == 0: all rows.
+  int has_rows;
+  int rows[2 * IGS_LOSS_MAX_ROW_VIEWS];
 };
+
+__device__ __forceinline__ void loss_row_range(const LossParams& p, int plane, int& r0, int& r1) {
+  r0 = 0; r1 = p.H;
+  if (p.has_rows) { const int v = plane / p.plane_per_view; r0 = p.rows[2 * v]; r1 = p.rows[2 * v + 1]; }
+}
 
 // Register-tiled separable filters on fp32x2 pairs.  The kernels are instruction-issue bound (ncu: DRAM 15-18 % of
 // peak), so
@@ -132,6 +142,12 @@ loss_pass1_kernel(LossParams p) {
   const size_t po = (size_t)plane * p.H * p.W;
   const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
   const int tid = threadIdx.x;
+  int r0, r1;
+  loss_row_range(p, plane, r0, r1);
+  if (y0 >= r1 || y0 + LOSS_BY <= r0) {  // no owned row in this tile (scratch and dpred were zero-filled by the launcher)
+    if (tid == 0) p.partial[((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = 0.0;
+    return;
+  }
   stage_pairs<VEC>(sxy, p.pred + po, p.gt + po, x0, y0, p.W, p.H, tid);
   __syncthreads();
   f32x2 w2[11];
@@ -215,7 +231,7 @@ loss_pass1_kernel(LossParams p) {
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int gy = y0 + rg * 4 + j;
-      if (gx >= p.W || gy >= p.H) continue;
+      if (gx >= p.W || gy >= r1 || gy < r0) continue;
       float mu1, mu2, e11, e22;
       unpack2(mA[j], mu1, mu2);
       unpack2(mB[j], e11, e22);
@@ -258,6 +274,9 @@ loss_pass2_kernel(LossParams p) {
   const size_t po = (size_t)plane * p.H * p.W;
   const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
   const int tid = threadIdx.x;
+  int r0, r1;
+  loss_row_range(p, plane, r0, r1);
+  if (y0 >= r1 + LOSS_R || y0 + LOSS_BY <= r0 - LOSS_R) return;  // dL/dpred is zero here (pre-filled by the launcher)
   stage_pairs<VEC>(s01, p.dmu1 + po, p.dE11 + po, x0, y0, p.W, p.H, tid);
   stage_scalar<VEC>(s2, p.dE12 + po, x0, y0, p.W, p.H, tid);
   __syncthreads();
@@ -327,7 +346,8 @@ loss_pass2_kernel(LossParams p) {
       unpack2(m01[j], g0, g1);
       const float dssim = g0 + 2.0f * xv * g1 + yv * m2[j];
       const float d = xv - yv;
-      const float sgn = (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f);   // torch: sign(0) = 0
+      float sgn = (d > 0.0f) ? 1.0f : ((d < 0.0f) ? -1.0f : 0.0f);   // torch: sign(0) = 0
+      if (gy < r0 || gy >= r1) sgn = 0.0f;                            // the L1 term of this row belongs to another rank
       O[o] = (p.lambda * sgn - (1.0f - p.lambda) * dssim) * p.inv_n;
     }
   }
@@ -356,9 +376,21 @@ size_t refine_loss_scratch_bytes(int V, int H, int W) {
 }
 
 void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float grad_scale,
-                        float* loss_sum,
+                        const int* loss_rows_host, float* loss_sum,
                         float* dpred, char* scratch, cudaStream_t s) {
   LossParams p;
+  p.has_rows = loss_rows_host != nullptr ? 1 : 0;
+  double owned_rows = (double)V * H;   // sum over views of the rows whose loss terms are computed here
+  if (p.has_rows) {
+    owned_rows = 0.0;
+    for (int v = 0; v < V; v++) {
+      int a = loss_rows_host[2 * v], b = loss_rows_host[2 * v + 1];
+      a = a < 0 ? 0 : (a > H ? H : a);
+      b = b < a ? a : (b > H ? H : b);
+      p.rows[2 * v] = a; p.rows[2 * v + 1] = b;
+      owned_rows += (double)(b - a);
+    }
+  }
   {
     float gf[11], fsum = 0;
     for (int x = 0; x < 11; x++) gf[x] = (float)exp(-(double)((x - 5) * (x - 5)) / (2.0 * 1.5 * 1.5));
@@ -375,6 +407,10 @@ void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W,
   size_t off = (3 * planes * N * sizeof(float) + 255) & ~size_t(255);
   p.partial = reinterpret_cast<double*>(scratch + off);
   dim3 grid((W + LOSS_BX - 1) / LOSS_BX, (H + LOSS_BY - 1) / LOSS_BY, V * 3);
+  if (p.has_rows) {  // rows nobody here owns: zero partials (pass 2 reads a 5-row halo of them) and zero dL/dpred
+    cudaMemsetAsync(p.dmu1, 0, 3 * planes * N * sizeof(float), s);
+    cudaMemsetAsync(dpred, 0, planes * N * sizeof(float), s);
+  }
   count_launch(3);
   // 16-byte staging loads need W % 4 == 0 (every float4 entirely inside or outside the image) and aligned planes
   const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(gt) |
@@ -388,7 +424,8 @@ void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W,
     loss_pass2_kernel<false><<<grid, 256, 0, s>>>(p);
   }
   size_t nblk = (size_t)grid.x * grid.y * grid.z;
-  loss_final_kernel<<<1, 256, 0, s>>>(p.partial, nblk, 1.0 / (3.0 * (double)H * (double)W), (double)V * (1.0 - (double)lambda),
+  // sum_v (1 - lambda) * mean(1 - ssim) = (1 - lambda) * (owned rows / H) - (1 - lambda) * sum(ssim) / (3 H W)
+  loss_final_kernel<<<1, 256, 0, s>>>(p.partial, nblk, 1.0 / (3.0 * (double)H * (double)W), owned_rows / (double)H * (1.0 - (double)lambda),
                                       loss_sum);
 }
 

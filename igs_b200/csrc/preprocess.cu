@@ -301,9 +301,10 @@ project_kernel(ProjectParams p, const Camera* __restrict__ cams, const float* __
       int ri = (int)my_radius;
       float rf = (float)ri;
       int rminx = min(p.tiles_x, max(0, (int)fmul(fsub(px, rf), 0.0625f)));
-      int rminy = min(p.tiles_y, max(0, (int)fmul(fsub(py, rf), 0.0625f)));
+      // rows are clipped to the view's tile-row window (the whole image unless the caller renders a band)
+      int rminy = min(cam.row1, max(cam.row0, (int)fmul(fsub(py, rf), 0.0625f)));
       int rmaxx = min(p.tiles_x, max(0, (int)fmul(fadd(fadd(fadd(px, rf), 16.0f), -1.0f), 0.0625f)));
-      int rmaxy = min(p.tiles_y, max(0, (int)fmul(fadd(fadd(fadd(py, rf), 16.0f), -1.0f), 0.0625f)));
+      int rmaxy = min(cam.row1, max(cam.row0, (int)fmul(fadd(fadd(fadd(py, rf), 16.0f), -1.0f), 0.0625f)));
       uint32_t area = (uint32_t)(rmaxx - rminx) * (uint32_t)(rmaxy - rminy);
       if (area != 0) {
         float rgb[3];

@@ -51,7 +51,8 @@ FwdRet forward_impl(const torch::Tensor& background, const torch::Tensor& means3
                     float scale_modifier, const torch::Tensor& cov3D_precomp, const torch::Tensor& viewmatrix,
                     const torch::Tensor& projmatrix, float tan_fovx, float tan_fovy, float kernel_size, int H, int W,
                     const torch::Tensor& sh, int degree, const torch::Tensor& campos, bool prefiltered,
-                    bool require_coord, bool require_depth, bool debug, int V, bool batched) {
+                    bool require_coord, bool require_depth, bool debug, int V, bool batched,
+                    const torch::Tensor& tile_rows = torch::Tensor()) {
   if (means3D.ndimension() != 2 || means3D.size(1) != 3) {
     AT_ERROR("means3D must have dimensions (num_points, 3)");
   }
@@ -64,6 +65,7 @@ FwdRet forward_impl(const torch::Tensor& background, const torch::Tensor& means3
   // One slab for the 15 output planes (the reference zero-fills 8 tensors separately).  With require_coord and
   // require_depth the blend kernel writes every pixel of every plane, so the slab needs no memset (1.6 GB at C3);
   // otherwise the planes that are not produced must read as zeros, like the reference's.
+  const bool windowed = tile_rows.defined() && tile_rows.numel() != 0;
   const bool all_planes_written = require_coord && require_depth && P != 0;
   torch::Tensor slab = all_planes_written ? torch::empty({(int64_t)V * 15, H, W}, fopt)
                                           : torch::zeros({(int64_t)V * 15, H, W}, fopt);
@@ -107,6 +109,13 @@ FwdRet forward_impl(const torch::Tensor& background, const torch::Tensor& means3
     a.out_mcoord = out_mcoord.data_ptr<float>(); a.out_depth = out_depth.data_ptr<float>();
     a.out_mdepth = out_mdepth.data_ptr<float>(); a.out_alpha = out_alpha.data_ptr<float>();
     a.out_normal = out_normal.data_ptr<float>(); a.radii = radii.data_ptr<int>();
+    torch::Tensor tr;
+    if (windowed) {
+      TORCH_CHECK(tile_rows.is_cuda() && tile_rows.scalar_type() == torch::kInt32 && tile_rows.numel() == (int64_t)V * 2,
+                  "tile_rows must be a CUDA int32 tensor [V,2]");
+      tr = tile_rows.contiguous();
+      a.tile_rows = tr.data_ptr<int>();
+    }
     TORCH_CHECK(a.background && a.opacities && a.viewmatrix && a.projmatrix && a.cam_pos, "missing required CUDA input");
     TORCH_CHECK(vm.numel() == (int64_t)V * 16 && pm.numel() == (int64_t)V * 16 && cp.numel() == (int64_t)V * 3,
                 "camera tensors must hold ", V, " view(s)");
@@ -249,11 +258,14 @@ FwdRet RasterizeViewsCUDA(const torch::Tensor& background, const torch::Tensor& 
                           const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices, const float tan_fovx,
                           const float tan_fovy, const float kernel_size, const int image_height, const int image_width,
                           const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
-                          const bool prefiltered, const bool require_coord, const bool require_depth, const bool debug) {
+                          const bool prefiltered, const bool require_coord, const bool require_depth, const bool debug,
+                          const c10::optional<torch::Tensor>& tile_rows_opt) {
+  const torch::Tensor tile_rows = tile_rows_opt.has_value() ? *tile_rows_opt : torch::Tensor();
   TORCH_CHECK(viewmatrices.dim() == 3, "viewmatrices must be [V,4,4]");
   return forward_impl(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                       viewmatrices, projmatrices, tan_fovx, tan_fovy, kernel_size, image_height, image_width, sh, degree,
-                      campos, prefiltered, require_coord, require_depth, debug, (int)viewmatrices.size(0), true);
+                      campos, prefiltered, require_coord, require_depth, debug, (int)viewmatrices.size(0), true,
+                      tile_rows);
 }
 
 BwdRet RasterizeViewsBackwardCUDA(
@@ -322,7 +334,7 @@ void AdamStep(torch::Tensor& param, const torch::Tensor& grad, torch::Tensor& ex
 }
 
 std::tuple<torch::Tensor, torch::Tensor> RefineLoss(const torch::Tensor& pred, const torch::Tensor& gt, double lambda_l1,
-                                                    double grad_scale) {
+                                                    double grad_scale, const std::vector<int64_t>& loss_rows) {
   TORCH_CHECK(pred.is_cuda() && gt.is_cuda(), "refine_loss needs CUDA tensors (there is no CPU path)");
   TORCH_CHECK(pred.dim() == 4 && pred.size(1) == 3 && pred.sizes() == gt.sizes(), "pred/gt must be [V,3,H,W]");
   TORCH_CHECK(pred.scalar_type() == torch::kFloat32 && gt.scalar_type() == torch::kFloat32, "float32 only");
@@ -331,9 +343,11 @@ std::tuple<torch::Tensor, torch::Tensor> RefineLoss(const torch::Tensor& pred, c
   torch::Tensor loss = torch::zeros({}, p.options());
   torch::Tensor dpred = torch::empty_like(p);
   torch::Tensor temp = torch::empty({0}, torch::TensorOptions().dtype(torch::kByte).device(p.device()));
+  TORCH_CHECK(loss_rows.empty() || (int64_t)loss_rows.size() == 2 * p.size(0), "loss_rows must hold 2 ints per view");
+  std::vector<int> rows(loss_rows.begin(), loss_rows.end());
   check(igs_refine_loss(p.data_ptr<float>(), g.data_ptr<float>(), (int)p.size(0), (int)p.size(2), (int)p.size(3),
-                        (float)lambda_l1, (float)grad_scale, loss.data_ptr<float>(), dpred.data_ptr<float>(), tensor_alloc,
-                        &temp,
+                        (float)lambda_l1, (float)grad_scale, rows.empty() ? nullptr : rows.data(), loss.data_ptr<float>(),
+                        dpred.data_ptr<float>(), tensor_alloc, &temp,
                         (void*)at::cuda::getCurrentCUDAStream().stream()),
         "refine_loss");
   return std::make_tuple(loss, dpred);
@@ -407,7 +421,9 @@ std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor> RefineGrad(
     const torch::Tensor& background, const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices,
     const torch::Tensor& campos, double tan_fovx, double tan_fovy, double kernel_size, double scale_modifier, int H,
     int W, int degree, const torch::Tensor& gt, int64_t total_views, double lambda_l1, bool require_coord,
-    bool require_depth, bool debug) {
+    bool require_depth, bool debug, const c10::optional<torch::Tensor>& tile_rows_opt,
+    const std::vector<int64_t>& loss_rows) {
+  const torch::Tensor tile_rows = tile_rows_opt.has_value() ? *tile_rows_opt : torch::Tensor();
   TORCH_CHECK(flat.is_cuda() && grad.is_cuda(), "refine_grad needs CUDA tensors (there is no CPU path)");
   TORCH_CHECK(flat.is_contiguous() && grad.is_contiguous() && flat.numel() == grad.numel(), "flat/grad must be contiguous and equal-sized");
   TORCH_CHECK(flat.scalar_type() == torch::kFloat32 && grad.scalar_type() == torch::kFloat32, "float32 only");
@@ -435,7 +451,7 @@ std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor> RefineGrad(
   torch::Tensor none;
   FwdRet f = forward_impl(background, xyz, none, op, sc, rot, (float)scale_modifier, none, viewmatrices, projmatrices,
                           (float)tan_fovx, (float)tan_fovy, (float)kernel_size, H, W, shs, degree, campos, false,
-                          require_coord, require_depth, debug, V, true);
+                          require_coord, require_depth, debug, V, true, tile_rows);
   const int rendered = std::get<0>(f);
   const torch::Tensor& color = std::get<1>(f);
   torch::Tensor loss = torch::zeros({}, flat.options());
@@ -444,8 +460,10 @@ std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor> RefineGrad(
   torch::Tensor gtc = gt.contiguous();
   TORCH_CHECK(gtc.is_cuda() && gtc.scalar_type() == torch::kFloat32, "gt must be a float32 CUDA tensor");
   const float gscale = 1.0f / (float)total_views;
+  TORCH_CHECK(loss_rows.empty() || (int64_t)loss_rows.size() == 2 * (int64_t)V, "loss_rows must hold 2 ints per view");
+  std::vector<int> rows(loss_rows.begin(), loss_rows.end());
   check(igs_refine_loss(color.data_ptr<float>(), gtc.data_ptr<float>(), V, H, W, (float)lambda_l1, gscale,
-                        loss.data_ptr<float>(), dcolor.data_ptr<float>(), tensor_alloc, &temp, (void*)stream),
+                        rows.empty() ? nullptr : rows.data(), loss.data_ptr<float>(), dcolor.data_ptr<float>(), tensor_alloc, &temp, (void*)stream),
         "refine_loss");
   BwdDest dest;
   dest.means3D = slice(grad, 0, 3, {P, 3});
@@ -513,8 +531,13 @@ std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> DensifyGather(
 
 PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("refine_loss", &RefineLoss, pybind11::arg("pred"), pybind11::arg("gt"), pybind11::arg("lambda_l1"),
-        pybind11::arg("grad_scale") = 1.0);
-  m.def("refine_grad", &RefineGrad);
+        pybind11::arg("grad_scale") = 1.0, pybind11::arg("loss_rows") = std::vector<int64_t>());
+  m.def("refine_grad", &RefineGrad, pybind11::arg("flat"), pybind11::arg("grad"), pybind11::arg("offs"), pybind11::arg("P"),
+        pybind11::arg("background"), pybind11::arg("viewmatrices"), pybind11::arg("projmatrices"), pybind11::arg("campos"),
+        pybind11::arg("tan_fovx"), pybind11::arg("tan_fovy"), pybind11::arg("kernel_size"), pybind11::arg("scale_modifier"),
+        pybind11::arg("H"), pybind11::arg("W"), pybind11::arg("degree"), pybind11::arg("gt"), pybind11::arg("total_views"),
+        pybind11::arg("lambda_l1"), pybind11::arg("require_coord"), pybind11::arg("require_depth"), pybind11::arg("debug"),
+        pybind11::arg("tile_rows") = pybind11::none(), pybind11::arg("loss_rows") = std::vector<int64_t>());
   m.def("activate_forward", &ActivateForward);
   m.def("activate_backward", &ActivateBackward);
   m.def("adam_step_groups", &AdamStepGroups);
@@ -523,7 +546,13 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
   m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
   m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
   m.def("mark_visible", &markVisible);
-  m.def("rasterize_views", &RasterizeViewsCUDA);
+  m.def("rasterize_views", &RasterizeViewsCUDA, pybind11::arg("background"), pybind11::arg("means3D"), pybind11::arg("colors"),
+        pybind11::arg("opacity"), pybind11::arg("scales"), pybind11::arg("rotations"), pybind11::arg("scale_modifier"),
+        pybind11::arg("cov3D_precomp"), pybind11::arg("viewmatrices"), pybind11::arg("projmatrices"),
+        pybind11::arg("tan_fovx"), pybind11::arg("tan_fovy"), pybind11::arg("kernel_size"), pybind11::arg("image_height"),
+        pybind11::arg("image_width"), pybind11::arg("sh"), pybind11::arg("degree"), pybind11::arg("campos"),
+        pybind11::arg("prefiltered"), pybind11::arg("require_coord"), pybind11::arg("require_depth"),
+        pybind11::arg("debug"), pybind11::arg("tile_rows") = pybind11::none());
   m.def("rasterize_views_backward", &RasterizeViewsBackwardCUDA);
   m.def("decode_buffers", &DecodeBuffers);
   m.def("adam_step", &AdamStep);

@@ -28,6 +28,8 @@ class MultiViewSettings(NamedTuple):
     require_depth: bool = True
     require_coord: bool = True
     debug: bool = False
+    tile_rows: Optional[torch.Tensor] = None   # [V,2] int32 CUDA: tile-row window rendered per view (None: whole image)
+    loss_rows: Optional[list] = None            # flat [2V] pixel rows whose loss terms this call owns (refine loop)
 
 
 class _RasterizeViews(torch.autograd.Function):
@@ -37,7 +39,8 @@ class _RasterizeViews(torch.autograd.Function):
         out = _C.rasterize_views(s.bg, means3D, e, opacities, scales, rotations, s.scale_modifier, e,
                                  s.viewmatrices, s.projmatrices, s.tanfovx, s.tanfovy, s.kernel_size,
                                  s.image_height, s.image_width, sh, s.sh_degree, s.campos, False,
-                                 s.require_coord, s.require_depth, s.debug)
+                                 s.require_coord, s.require_depth, s.debug,
+                                 s.tile_rows)
         num_rendered, color, coord, mcoord, alpha, normal, depth, mdepth, radii, geom, binning, img = out
         ctx.s = s
         ctx.num_rendered = num_rendered

@@ -133,20 +133,22 @@ class _FusedLoss(torch.autograd.Function):
     """Sum over views of the per-view refine loss, value and dL/dpred from csrc/loss.cu."""
 
     @staticmethod
-    def forward(ctx, pred, gt, lambda_l1):
-        loss_sum, dpred = _C.refine_loss(pred, gt, float(lambda_l1), 1.0)
+    def forward(ctx, pred, gt, lambda_l1, loss_rows=None):
+        loss_sum, dpred = _C.refine_loss(pred, gt, float(lambda_l1), 1.0, list(loss_rows) if loss_rows else [])
         ctx.save_for_backward(dpred)
         return loss_sum
 
     @staticmethod
     def backward(ctx, g):
         (dpred,) = ctx.saved_tensors
-        return dpred * g, None, None
+        return dpred * g, None, None, None
 
 
-def refine_loss_sum(pred, gt, lambda_l1=0.8, impl="fused"):
+def refine_loss_sum(pred, gt, lambda_l1=0.8, impl="fused", loss_rows=None):
     if impl == "fused":
-        return _FusedLoss.apply(pred.contiguous(), gt.contiguous(), lambda_l1)
+        return _FusedLoss.apply(pred.contiguous(), gt.contiguous(), lambda_l1, loss_rows)
+    if loss_rows:
+        raise ValueError("row-restricted losses need the fused loss kernel")
     return refine_loss_torch(pred, gt, lambda_l1).sum()
 
 
@@ -188,7 +190,8 @@ def refine_iteration(state: RefineState, settings: MultiViewSettings, gt: torch.
             state.flat, state.grad, state.offsets(), state.P, s.bg, s.viewmatrices, s.projmatrices, s.campos,
             float(s.tanfovx), float(s.tanfovy), float(s.kernel_size), float(s.scale_modifier), int(s.image_height),
             int(s.image_width), int(s.sh_degree), gt, int(total_views), float(lambda_l1), bool(s.require_coord),
-            bool(s.require_depth), bool(s.debug))
+            bool(s.require_depth), bool(s.debug), s.tile_rows,
+            list(s.loss_rows) if s.loss_rows else [])
         loss = reduce_gradients(state.grad, loss, group)
         if do_step:
             state.adam_step()
@@ -205,7 +208,7 @@ def refine_iteration(state: RefineState, settings: MultiViewSettings, gt: torch.
         opac = torch.sigmoid(lv["opacity"])
         outs = rasterize_views(lv["xyz"], lv["shs"], opac, scales, rot, settings)
         color, radii = outs[0], outs[1]
-        loss = refine_loss_sum(color, gt, lambda_l1, loss_impl) / float(total_views)
+        loss = refine_loss_sum(color, gt, lambda_l1, loss_impl, settings.loss_rows) / float(total_views)
         grads = torch.autograd.grad(loss, leaves, allow_unused=True)
         for n, g in zip(names, grads):
             a, b, _k = state.slices[n]
@@ -261,3 +264,70 @@ def shard_views_balanced(costs, rank: int, world: int):
 def shard_views(total_views: int, rank: int, world: int):
     """View v -> rank v mod world: 20 views on 8 ranks = 3,3,3,3,2,2,2,2."""
     return list(range(rank, total_views, world))
+
+
+# ------------------------------------------------------------------------------------------------
+# finer than whole views: bands of tile rows
+# ------------------------------------------------------------------------------------------------
+SSIM_RADIUS = 5   # 11x11 window: the loss terms of a pixel row read rendered rows +- 5
+
+
+class Unit(NamedTuple):
+    """A band of one view owned by a rank: its loss terms are those of pixel rows [row0, row1)."""
+    view: int
+    row0: int
+    row1: int
+
+
+def shard_units(total_views: int, height: int, rank: int, world: int):
+    """Whole views when `world` divides `total_views`; otherwise every view is cut into world/gcd(total_views, world)
+    bands of tile rows so that all ranks get the same number of bands (20 views on 8 ranks: 40 half-views, 5 per rank
+    = 2.5 views each instead of 3,3,3,3,2,2,2,2).  A rank's bands are contiguous in (view, band) order and adjacent
+    bands of one view are merged.  Each band's tile-row window is widened by the SSIM radius (`unit_windows`), and
+    per-pixel results inside a window are identical to the full render, so the sum over ranks of the band losses /
+    gradients equals the single-rank step (tests/test_refine_gpu.py)."""
+    if world <= 1 or total_views % world == 0:
+        return [Unit(v, 0, height) for v in range(rank, total_views, world)] if world > 1 else \
+               [Unit(v, 0, height) for v in range(total_views)]
+    parts = world // math.gcd(total_views, world)
+    tile_rows = (height + 15) // 16
+    if parts > tile_rows:
+        return [Unit(v, 0, height) for v in range(rank, total_views, world)]
+    n_units = total_views * parts
+    lo, hi = rank * n_units // world, (rank + 1) * n_units // world
+    units = []
+    for u in range(lo, hi):
+        v, k = divmod(u, parts)
+        r0 = min(height, 16 * (k * tile_rows // parts))
+        r1 = min(height, 16 * ((k + 1) * tile_rows // parts))
+        if units and units[-1].view == v and units[-1].row1 == r0:
+            units[-1] = Unit(v, units[-1].row0, r1)
+        else:
+            units.append(Unit(v, r0, r1))
+    return units
+
+
+def unit_windows(units, height: int):
+    """(tile_rows [U,2] int32 CPU tensor, loss_rows flat list) for `units`: the tile-row window that must be rendered
+    so that rows [row0 - 5, row1 + 5) are exact, and the rows whose loss terms the unit owns.  (None, None) when every
+    unit is a whole view."""
+    if all(u.row0 == 0 and u.row1 >= height for u in units):
+        return None, None
+    t_all = (height + 15) // 16
+    tr, lr = [], []
+    for u in units:
+        tr.append([max(0, (u.row0 - SSIM_RADIUS) // 16), min(t_all, (u.row1 + SSIM_RADIUS + 15) // 16)])
+        lr += [u.row0, u.row1]
+    return torch.tensor(tr, dtype=torch.int32), lr
+
+
+def settings_for_units(all_views: MultiViewSettings, units) -> MultiViewSettings:
+    """The MultiViewSettings of a rank that owns `units` of the views in `all_views` (one entry per unit: a view that
+    is split appears once per band).  The matching targets are `gt_all[[u.view for u in units]]`."""
+    idx = torch.tensor([u.view for u in units], dtype=torch.long, device=all_views.viewmatrices.device)
+    tr, lr = unit_windows(units, int(all_views.image_height))
+    return all_views._replace(viewmatrices=all_views.viewmatrices[idx].contiguous(),
+                              projmatrices=all_views.projmatrices[idx].contiguous(),
+                              campos=all_views.campos[idx].contiguous(),
+                              tile_rows=None if tr is None else tr.to(all_views.viewmatrices.device),
+                              loss_rows=lr)

@@ -57,7 +57,7 @@
 extern "C" {
 #endif
 
-#define IGS_RASTER_ABI_VERSION 3
+#define IGS_RASTER_ABI_VERSION 4
 
 typedef enum igs_status {
   IGS_OK = 0,
@@ -94,7 +94,8 @@ typedef struct igs_forward_args {
   int prefiltered;             /* must be 0                            */
   int require_coord, require_depth;
   int debug;                   /* 1: synchronise + check after every stage          */
-  /* outputs, all pre-zeroed by the caller like the reference's torch::full(0) */
+  /* outputs; every pixel of every requested map is written, maps that are NOT requested (require_coord /
+   * require_depth = 0) are left untouched and must be pre-zeroed by the caller to read like the reference's */
   float* out_color;   /* [V][3][H][W] */
   float* out_coord;   /* [V][3][H][W] */
   float* out_mcoord;  /* [V][3][H][W] */
@@ -103,6 +104,12 @@ typedef struct igs_forward_args {
   float* out_alpha;   /* [V][1][H][W] */
   float* out_normal;  /* [V][3][H][W] */
   int* radii;         /* [V][P]       */
+  /* Optional (NULL = whole image): DEVICE array [V][2] of tile-row windows {row_begin, row_end} in units of 16-pixel
+   * tile rows.  View v is binned and blended only in tile rows [row_begin, row_end); pixels outside receive the
+   * background, radii report visibility inside the window, and backward returns the gradient of exactly the rendered
+   * pixels.  Per-pixel results inside the window are identical to the full render.  Used to shard ONE view over
+   * several GPUs (igs_b200.refine.shard_units); the reference has no equivalent. */
+  const int* tile_rows;
 } igs_forward_args;
 
 /* Forward.  *num_rendered receives R = total number of (Gaussian, tile) instances over all views
@@ -211,10 +218,13 @@ int igs_adam_step_groups(float* param, const float* grad, float* exp_avg, float*
  *   *loss_sum = sum_v [ lambda * mean|pred_v - gt_v| + (1 - lambda) * (1 - mean SSIM(pred_v, gt_v)) ]
  *   dL_dpred  = grad_scale * d(*loss_sum) / d(pred)     (11x11 Gaussian window, sigma 1.5, zero padding)
  * grad_scale is the upstream gradient of loss_sum (1/total_views when the step's loss is the mean over views);
- * loss_sum itself is NOT scaled.  loss_sum is a DEVICE float; temp_alloc provides 36*V*H*W bytes (+ a few KB). */
+ * loss_sum itself is NOT scaled.  loss_sum is a DEVICE float; temp_alloc provides 36*V*H*W bytes (+ a few KB).
+ * loss_rows: optional HOST array [V][2] (NULL = every row; V <= 64 otherwise): only the loss terms (L1 and SSIM-map
+ * pixels) of rows [loss_rows[2v], loss_rows[2v+1]) of view v are summed — the share of a rank that renders a band of
+ * the view (igs_forward_args.tile_rows must then cover these rows +- 5, the SSIM window radius). */
 int igs_refine_loss(const float* pred, const float* gt, int V, int height, int width, float lambda_l1,
-                    float grad_scale, float* loss_sum, float* dL_dpred, igs_alloc_fn temp_alloc, void* temp_user,
-                    void* stream);
+                    float grad_scale, const int* loss_rows, float* loss_sum, float* dL_dpred, igs_alloc_fn temp_alloc,
+                    void* temp_user, void* stream);
 
 /* Parameter activations of the refine loop and their chain rule (igs/models/gaussian_model.py:89-127, i.e.
  * RaDe-GS scene/gaussian_model.py setup_functions: scaling = exp, rotation = F.normalize (eps 1e-12),

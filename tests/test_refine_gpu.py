@@ -200,3 +200,51 @@ def test_grouped_adam_matches_per_group_adam(cuda_dev, native):
             native.adam_step(b[off:off + sz], g[off:off + sz], mb[off:off + sz], vb[off:off + sz], lr, 0.9, 0.999, 1e-15, step)
             off += sz
         assert torch.equal(a, b) and torch.equal(ma, mb) and torch.equal(va, vb)
+
+
+def test_tile_row_window_equals_full_render_inside(cuda_dev, native):
+    """A view rendered only in a band of tile rows: identical pixels inside the band, background outside, fewer
+    instances; radii report visibility inside the band."""
+    from igs_b200.multiview import rasterize_views
+    P, V, W, H = 6000, 2, 176, 200
+    state, st = _state_and_settings(cuda_dev, P, V, W, H)
+    sc, rot, op = native.activate_forward(state.param("scaling"), state.param("rotation"), state.param("opacity"))
+    full = rasterize_views(state.param("xyz"), state.param("shs"), op, sc, rot, st)
+    rows = torch.tensor([[3, 9], [0, 5]], dtype=torch.int32, device=cuda_dev)
+    band = rasterize_views(state.param("xyz"), state.param("shs"), op, sc, rot, st._replace(tile_rows=rows))
+    for v, (a, b) in enumerate(rows.tolist()):
+        y0, y1 = 16 * a, min(H, 16 * b)
+        for k in (0, 2, 3, 4, 5, 6, 7):   # colour, coord, mcoord, depth, mdepth, alpha, normal
+            assert torch.equal(band[k][v][:, y0:y1], full[k][v][:, y0:y1]), (v, k)
+        outside = torch.cat([band[0][v][:, :y0], band[0][v][:, y1:]], dim=1)
+        assert float(outside.abs().max()) == 0.0 and float(band[6][v].sum() - band[6][v][:, y0:y1].sum()) == 0.0
+        assert bool(((band[1][v] > 0) <= (full[1][v] > 0)).all()) and int((band[1][v] > 0).sum()) < int((full[1][v] > 0).sum())
+
+
+@pytest.mark.parametrize("world", [2, 4])
+def test_band_sharded_step_equals_single_rank_step(cuda_dev, native, world):
+    """3 views on 2 / 4 ranks do not divide: shard_units cuts the views into bands of tile rows.  The sum over ranks
+    of the band losses and packed gradients equals the one-rank step on all views."""
+    from igs_b200 import refine
+    P, V, W, H = 12000, 3, 176, 200
+    state, st_all = _state_and_settings(cuda_dev, P, V, W, H)
+    gen = torch.Generator().manual_seed(21)
+    gt = torch.rand(V, 3, H, W, generator=gen).to(cuda_dev)
+    r_all = refine.refine_iteration(state, st_all, gt, V, do_step=False)
+    g_all = state.grad.clone()
+    total = torch.zeros_like(g_all)
+    loss, rendered, split = 0.0, 0, False
+    for rank in range(world):
+        units = refine.shard_units(V, H, rank, world)
+        split |= any(u.row0 > 0 or u.row1 < H for u in units)
+        st = refine.settings_for_units(st_all, units)
+        r = refine.refine_iteration(state, st, gt[[u.view for u in units]], V, do_step=False)
+        total += state.grad
+        loss += float(r.loss)
+        rendered += r.num_rendered
+    assert split
+    assert abs(loss - float(r_all.loss)) <= 1e-5 * abs(loss)
+    for name, _ in refine.GROUPS:
+        a, b, _k = state.slices[name]
+        assert float((total[a:b] - g_all[a:b]).abs().max()) <= 2e-4 * float(g_all[a:b].abs().max()), name
+    assert rendered < 1.35 * r_all.num_rendered   # the halo rows are the only duplicated work
