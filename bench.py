@@ -53,6 +53,8 @@ def parse():
     ap.add_argument("--no-ref-cuda", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--cpu-sample-views", type=int, default=1)
+    ap.add_argument("--no-bands", dest="bands", action="store_false",
+                    help="shard whole views only (v mod N) even when N does not divide the number of views")
     ap.add_argument("--no-balance", dest="balance", action="store_false",
                     help="assign view v to rank v mod N instead of balancing by per-view instance counts")
     return ap.parse_args()
@@ -296,6 +298,18 @@ def main():
         costs = measure_view_costs(cfg, cams, sc, torch.device("cuda", local_rank))
         my_views = refine.shard_views_balanced(costs, rank, world)
         assignment = "LPT on per-view instance counts"
+    # N does not divide the views (20 views on 8 GPUs): cut the views into bands of tile rows so that every rank
+    # renders the same share (2.5 views) instead of 3,3,3,3,2,2,2,2 (igs_b200.refine.shard_units)
+    tile_rows_dev, loss_rows = None, None
+    band_share = None
+    if world > 1 and args.bands and V % world != 0:
+        units = refine.shard_units(V, H, rank, world)
+        my_views = [u.view for u in units]
+        tr, loss_rows = refine.unit_windows(units, H)
+        if tr is not None:
+            tile_rows_dev = tr.to(dev)
+            band_share = sum(u.row1 - u.row0 for u in units) / float(H)
+            assignment = f"bands of tile rows: {len(units)} units = {band_share:.2f} views per rank (shard_units)"
     Vl = len(my_views)
     g = torch.Generator().manual_seed(2 + 1000 * rank)
     gt_host = torch.rand(max(Vl, 1), 3, H, W, generator=g).pin_memory()
@@ -315,7 +329,8 @@ def main():
         cp = cam_flat[Vl * 32:].view(Vl, 3)
         return MultiViewSettings(image_height=H, image_width=W, tanfovx=cams.tanfovx, tanfovy=cams.tanfovy,
                                  kernel_size=0.0, bg=bg, scale_modifier=1.0, viewmatrices=vm, projmatrices=pm,
-                                 sh_degree=3, campos=cp, require_depth=True, require_coord=True, debug=False)
+                                 sh_degree=3, campos=cp, require_depth=True, require_coord=True, debug=False,
+                                 tile_rows=tile_rows_dev, loss_rows=loss_rows)
 
     cam_dev.copy_(cam_host)
     gt_dev.copy_(gt_host)
@@ -426,13 +441,14 @@ def main():
     loss_val = float(last.loss.item())
     # per-rank load (views, instances, device ms spent in this library's stages per step)
     my_ms = sum(ms for _n, ms, c in stages if c > 0) / args.steps
-    per_rank = torch.tensor([float(Vl), float(R_local), my_ms], device=dev, dtype=torch.float64)
+    per_rank = torch.tensor([float(band_share if band_share is not None else Vl), float(R_local), my_ms], device=dev,
+                            dtype=torch.float64)
     if world > 1:
         allr = [torch.zeros_like(per_rank) for _ in range(world)]
         dist.all_gather(allr, per_rank)
     else:
         allr = [per_rank]
-    per_rank = [{"views": int(t[0]), "R": int(t[1]), "stage_ms": round(float(t[2]), 3)} for t in allr]
+    per_rank = [{"views": round(float(t[0]), 2), "R": int(t[1]), "stage_ms": round(float(t[2]), 3)} for t in allr]
 
     # ---- (2) forward-only throughput ----
     def fwd_only():
@@ -449,7 +465,8 @@ def main():
             sc_a, rot_a, op_a = _C.activate_forward(state.param("scaling"), state.param("rotation"), state.param("opacity"))
             e_ = torch.empty(0, device=dev)
             o = _C.rasterize_views(st.bg, state.param("xyz"), e_, op_a, sc_a, rot_a, 1.0, e_, st.viewmatrices, st.projmatrices,
-                                   st.tanfovx, st.tanfovy, 0.0, H, W, state.param("shs"), 3, st.campos, False, True, True, False)
+                                   st.tanfovx, st.tanfovy, 0.0, H, W, state.param("shs"), 3, st.campos, False, True, True, False,
+                                   st.tile_rows)
             dec = _C.decode_buffers(P, Vl, o[0], H, W, o[9], o[10], o[11])
             E_local = dec[3].view(Vl, 2, H * W)[:, 0].to(torch.int64).sum()
             R_cnt = torch.tensor(int(o[0]), device=dev, dtype=torch.int64)
@@ -497,6 +514,7 @@ def main():
         peak, peak_src = 6650.0, "fallback (B200_PROFILING.md)"
     stage_ms = {n: (ms, c) for n, ms, c in stages if c > 0}
     VP = Vl * P
+    Vpix = band_share if band_share is not None else Vl   # views' worth of pixels this rank blends
     R = R_local
     # tile-id sort: 8-bit digits, or 9-bit when that saves a pass (binning.cu radix_sort_pairs)
     tile_bits = max(1, (max(1, Vl) * ((W + 15) // 16) * ((H + 15) // 16) - 1).bit_length())
@@ -510,12 +528,12 @@ def main():
         "emit": VP * (4 + 8 + 32 + 4) + R * 12,
         "tile_sort": sort_passes * R * (8 + 8) + sort_passes * R * 4,
         "finalize_bins": R * (4 + 4 + 4 + 4),
-        "blend_fwd": R * (4 + 32 + 64) + Vl * N * 88,
-        "blend_bwd": R * (4 + 4 + 32 + 4) + Vl * N * (12 + 4 + 8) + R * 64,
+        "blend_fwd": R * (4 + 32 + 64) + Vpix * N * 88,
+        "blend_bwd": R * (4 + 4 + 32 + 4) + Vpix * N * (12 + 4 + 8) + R * 64,
         "gather_bwd": R * 64 + VP * (32 + 4 + 4 + 8 + 1 + 12 + 64),
         "finish_bwd": VP * 64 + P * (12 + 192 + 12 + 16 + 12 + 4 + 24 + 192 + 12 + 16),
         "adam": P * 59 * 4 * 7,
-        "loss": Vl * N * 3 * 4 * 3,
+        "loss": Vpix * N * 3 * 4 * 3,
         "activate": P * 80,   # mean of the forward (64 B/Gaussian) and backward (96 B/Gaussian) launches
     }
     top = max(stage_ms.items(), key=lambda kv: kv[1][0])[0] if stage_ms else None
@@ -539,7 +557,7 @@ def main():
         if tf.exists() and clocks and clocks.get("sm_mhz"):
             wi = json.loads(tf.read_text()).get("_warp_instructions_per_launch", {}).get(top)
             if wi and args.workload == "C3":
-                wi = wi * (Vl / float(V))
+                wi = wi * ((band_share if band_share is not None else Vl) / float(V))
                 sms = torch.cuda.get_device_properties(dev).multi_processor_count
                 peak_issue = 4.0 * sms * clocks["sm_mhz"] * 1e6
                 ach = wi / (per_launch_ms / 1e3)
