@@ -1,0 +1,96 @@
+"""GPU: the key-frame streaming refine loop (igs_b200/stream.py) against the loop a reference user writes
+(infer_batch.py:279-324: drop-in rasterizer module + torch loss + torch.optim.Adam), and end to end."""
+import random
+
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+
+def _setup(dev, P, V, W, H):
+    from igs_b200 import refine, scenes
+    from igs_b200.multiview import MultiViewSettings
+    sc = scenes.make_gaussians(P, 0, -1.8)
+    cams = scenes.make_cameras(V, W, H, 1)
+    st = MultiViewSettings(H, W, cams.tanfovx, cams.tanfovy, 0.0, torch.zeros(3, device=dev), 1.0,
+                           cams.viewmatrix.to(dev).contiguous(), cams.projmatrix.to(dev).contiguous(), 3,
+                           cams.campos.to(dev).contiguous())
+    state = refine.RefineState(sc.xyz, sc.log_scale, sc.rot, sc.opacity_logit, sc.sh, dev)
+    return sc, cams, st, state
+
+
+def test_keyframe_loop_matches_reference_users_loop(cuda_dev, native):
+    """Same draws, same loss, same Adam: after 6 single-view iterations the parameters of the native loop and of the
+    reference-style loop (drop-in module through autograd, refine_loss_torch, torch Adam eps=1e-15) agree."""
+    import diff_gaussian_rasterization_rade as dgr
+    from igs_b200 import refine, stream
+    P, V, W, H, iters = 8000, 4, 160, 120, 6
+    sc, cams, st, state = _setup(cuda_dev, P, V, W, H)
+    gt = torch.rand(V, 3, H, W, generator=torch.Generator().manual_seed(7)).to(cuda_dev)
+    cfg = stream.StreamConfig(refine_iterations=iters)
+    res = stream.refine_keyframe(state, st, gt, cfg, random.Random(5))
+
+    params = dict(xyz=sc.xyz, shs=sc.sh, scaling=sc.log_scale, rotation=sc.rot, opacity=sc.opacity_logit)
+    params = {k: v.to(cuda_dev).clone().requires_grad_(True) for k, v in params.items()}
+    lrs = refine.DEFAULT_LRS
+    opt = torch.optim.Adam([{"params": [params[k]], "lr": lrs[k]} for k in params], lr=0.0, eps=1e-15)
+    losses = []
+    for (v,) in stream.view_schedule(V, iters, random.Random(5)):
+        rs = dgr.GaussianRasterizationSettings(
+            image_height=H, image_width=W, tanfovx=cams.tanfovx, tanfovy=cams.tanfovy, kernel_size=0.0,
+            bg=torch.zeros(3, device=cuda_dev), scale_modifier=1.0, viewmatrix=st.viewmatrices[v],
+            projmatrix=st.projmatrices[v], sh_degree=3, campos=st.campos[v], prefiltered=False, require_depth=True,
+            require_coord=True, debug=False)
+        m2 = torch.zeros_like(params["xyz"], requires_grad=True)
+        out = dgr.GaussianRasterizer(raster_settings=rs)(
+            means3D=params["xyz"], means2D=m2, opacities=torch.sigmoid(params["opacity"]), shs=params["shs"],
+            scales=torch.exp(params["scaling"]), rotations=F.normalize(params["rotation"]))
+        loss = refine.refine_loss_torch(out[0].unsqueeze(0), gt[v:v + 1]).sum()
+        loss.backward()
+        opt.step()
+        opt.zero_grad(set_to_none=True)
+        losses.append(float(loss))
+    assert [s[0] for s in res.schedule] == [s[0] for s in stream.view_schedule(V, iters, random.Random(5))]
+    got = res.losses.cpu().tolist()
+    assert max(abs(a - b) for a, b in zip(got, losses)) <= 2e-4 * max(losses), (got, losses)
+    # Adam's first steps move every touched parameter by ~lr regardless of the gradient's size, so compare against
+    # the distance travelled: the two loops must agree far better than either moved
+    for name in ("xyz", "shs", "opacity", "scaling", "rotation"):
+        a = state.param(name).reshape(-1)
+        b = params[name].detach().reshape(-1)
+        moved = float((b - dict(xyz=sc.xyz, shs=sc.sh, scaling=sc.log_scale, rotation=sc.rot,
+                                opacity=sc.opacity_logit)[name].to(cuda_dev).reshape(-1)).abs().mean())
+        assert float((a - b).abs().mean()) <= 0.05 * moved, (name, float((a - b).abs().mean()), moved)
+
+
+def test_keyframe_loop_densifies_like_the_reference_schedule(cuda_dev, native):
+    from igs_b200 import stream
+    P, V, W, H = 6000, 3, 160, 120
+    _sc, _cams, st, state = _setup(cuda_dev, P, V, W, H)
+    gt = torch.rand(V, 3, H, W, generator=torch.Generator().manual_seed(8)).to(cuda_dev)
+    cfg = stream.StreamConfig(refine_iterations=45, use_densify=True, max_num=7000, radius=10.0,
+                              densify_grad_threshold=1e-7)
+    gen = torch.Generator(device=cuda_dev).manual_seed(1)
+    res = stream.refine_keyframe(state, st, gt, cfg, random.Random(2), generator=gen)
+    assert res.densified_at == [20, 40]
+    assert res.P == state.P and state.P != P and state.P <= 7000 + 2 * 7000   # bounded growth, pruned parents
+    assert state.step == 45 - 2          # no Adam step in the two densify iterations (grad=None in the reference)
+    assert state.flat.numel() == state.P * 59 and bool(torch.isfinite(state.flat).all())
+    assert bool(torch.isfinite(res.losses).all())
+
+
+def test_stream_improves_psnr_and_carries_gaussians(cuda_dev, native):
+    from igs_b200 import refine, stream
+    P, V, W, H = 10000, 4, 160, 120
+    _sc, _cams, st, state = _setup(cuda_dev, P, V, W, H)
+    with torch.no_grad():
+        target = refine.forward_views(state, st)[0].clamp(0, 1).cpu()
+    state.param("shs").add_(0.3 * torch.randn(P, 16, 3, generator=torch.Generator().manual_seed(3)).to(cuda_dev))
+    before = float(stream.psnr(stream.render_view(state, st, 0), target[0].to(cuda_dev)))
+    frames = [target.pin_memory() for _ in range(3)]
+    res = stream.run_stream(state, st, frames, stream.StreamConfig(refine_iterations=20), seed=0)
+    assert len(res.psnrs) == 3 and res.iterations == 60 and res.points_num == [P] * 3
+    assert res.psnrs[0] > before + 1.0 and res.psnrs[-1] >= res.psnrs[0] - 0.5
+    assert all(t > 0 for t in res.keyframe_ms)
