@@ -158,6 +158,29 @@ int igs_refine_loss(const float* pred, const float* gt, int V, int height, int w
   return IGS_OK;
 }
 
+int igs_depth_normal_loss(int use_coord, const float* map0, const float* map1, const float* normal, int V, int height,
+                          int width, float tan_fovx, float tan_fovy, float depth_ratio, float grad_scale,
+                          float* loss_sum, float* dL_dmap0, float* dL_dmap1, float* dL_dnormal, igs_alloc_fn temp_alloc,
+                          void* temp_user, void* stream) {
+  if (V < 0 || height <= 0 || width <= 0 || !temp_alloc || !(tan_fovx > 0.0f) || !(tan_fovy > 0.0f)) {
+    set_error("bad argument");
+    return IGS_ERR_INVALID;
+  }
+  if (V > 65535) { set_error("at most 65535 views per call"); return IGS_ERR_UNSUPPORTED; }
+  if (V == 0) return IGS_OK;
+  if (!map0 || !map1 || !normal || !loss_sum || !dL_dmap0 || !dL_dmap1 || !dL_dnormal) { set_error("null pointer"); return IGS_ERR_INVALID; }
+  char* tmp = temp_alloc(temp_user, geo_loss_scratch_bytes(V, height, width) + 256);
+  if (!tmp) { set_error("temp allocator returned NULL"); return IGS_ERR_ALLOC; }
+  tmp = (char*)(((uintptr_t)tmp + 255) & ~uintptr_t(255));
+  {
+    StageScope st(IGS_STAGE_LOSS, (cudaStream_t)stream);
+    launch_geo_loss(use_coord != 0, map0, map1, normal, V, height, width, tan_fovx, tan_fovy, depth_ratio, grad_scale,
+                    loss_sum, dL_dmap0, dL_dmap1, dL_dnormal, tmp, (cudaStream_t)stream);
+  }
+  IGS_CUDA_CHECK(cudaGetLastError());
+  return IGS_OK;
+}
+
 void igs_stage_timing_enable(int on) {
   std::lock_guard<std::mutex> lk(igs::g_timer.mu);
   igs::g_timer.on = on != 0;

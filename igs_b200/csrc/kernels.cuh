@@ -130,6 +130,10 @@ void launch_finish_bwd(const FinishBwdParams& p, cudaStream_t s);
 size_t refine_loss_scratch_bytes(int V, int H, int W);
 void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W, float lambda, float grad_scale, const int* loss_rows_host, float* loss_sum,
                         float* dpred, char* scratch, cudaStream_t s);
+size_t geo_loss_scratch_bytes(int V, int H, int W);
+void launch_geo_loss(bool coord, const float* m0, const float* m1, const float* normal, int V, int H, int W, float tan_fovx,
+                     float tan_fovy, float depth_ratio, float grad_scale, float* loss_sum, float* d_m0, float* d_m1,
+                     float* d_normal, char* scratch, cudaStream_t s);
 void launch_activate_fwd(int P, const float* log_scales, const float* raw_rot, const float* logit, float* scales,
                          float* rot, float* opac, cudaStream_t s);
 void launch_activate_bwd(int P, const float* scales, const float* raw_rot, const float* opac, const float* dL_dscales,

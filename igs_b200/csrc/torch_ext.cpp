@@ -353,6 +353,31 @@ std::tuple<torch::Tensor, torch::Tensor> RefineLoss(const torch::Tensor& pred, c
   return std::make_tuple(loss, dpred);
 }
 
+// (loss_sum, dL_dmap0, dL_dmap1, dL_dnormal) of the depth-normal consistency loss (igs_depth_normal_loss); maps are
+// [V,1,H,W] / [V,H,W] depths or [V,3,H,W] coords, normal [V,3,H,W]
+std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor> DepthNormalLoss(
+    const torch::Tensor& map0, const torch::Tensor& map1, const torch::Tensor& normal, bool use_coord, double tan_fovx,
+    double tan_fovy, double depth_ratio, double grad_scale) {
+  TORCH_CHECK(map0.is_cuda() && map1.is_cuda() && normal.is_cuda(), "depth_normal_loss needs CUDA tensors (there is no CPU path)");
+  TORCH_CHECK(normal.dim() == 4 && normal.size(1) == 3, "normal must be [V,3,H,W]");
+  TORCH_CHECK(map0.scalar_type() == torch::kFloat32 && map1.scalar_type() == torch::kFloat32 &&
+              normal.scalar_type() == torch::kFloat32, "float32 only");
+  const int64_t V = normal.size(0), H = normal.size(2), W = normal.size(3);
+  const int64_t want = V * (use_coord ? 3 : 1) * H * W;
+  TORCH_CHECK(map0.numel() == want && map1.numel() == want, "maps must hold V*", use_coord ? 3 : 1, "*H*W floats");
+  const c10::cuda::CUDAGuard guard(normal.device());
+  torch::Tensor a = map0.contiguous(), b = map1.contiguous(), n = normal.contiguous();
+  torch::Tensor loss = torch::zeros({}, n.options());
+  torch::Tensor da = torch::empty_like(a), db = torch::empty_like(b), dn = torch::empty_like(n);
+  torch::Tensor temp = torch::empty({0}, torch::TensorOptions().dtype(torch::kByte).device(n.device()));
+  check(igs_depth_normal_loss(use_coord ? 1 : 0, a.data_ptr<float>(), b.data_ptr<float>(), n.data_ptr<float>(), (int)V, (int)H,
+                              (int)W, (float)tan_fovx, (float)tan_fovy, (float)depth_ratio, (float)grad_scale,
+                              loss.data_ptr<float>(), da.data_ptr<float>(), db.data_ptr<float>(), dn.data_ptr<float>(),
+                              tensor_alloc, &temp, (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "depth_normal_loss");
+  return std::make_tuple(loss, da, db, dn);
+}
+
 // Adam over the packed parameter record: one launch for all groups.
 void AdamStepGroups(torch::Tensor& param, const torch::Tensor& grad, torch::Tensor& exp_avg, torch::Tensor& exp_avg_sq,
                     const std::vector<int64_t>& sizes, const std::vector<double>& lrs, double beta1, double beta2,
@@ -538,6 +563,9 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         pybind11::arg("H"), pybind11::arg("W"), pybind11::arg("degree"), pybind11::arg("gt"), pybind11::arg("total_views"),
         pybind11::arg("lambda_l1"), pybind11::arg("require_coord"), pybind11::arg("require_depth"), pybind11::arg("debug"),
         pybind11::arg("tile_rows") = pybind11::none(), pybind11::arg("loss_rows") = std::vector<int64_t>());
+  m.def("depth_normal_loss", &DepthNormalLoss, pybind11::arg("map0"), pybind11::arg("map1"), pybind11::arg("normal"),
+        pybind11::arg("use_coord"), pybind11::arg("tan_fovx"), pybind11::arg("tan_fovy"), pybind11::arg("depth_ratio") = 0.6,
+        pybind11::arg("grad_scale") = 1.0);
   m.def("activate_forward", &ActivateForward);
   m.def("activate_backward", &ActivateBackward);
   m.def("adam_step_groups", &AdamStepGroups);

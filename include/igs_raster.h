@@ -20,6 +20,8 @@
  *   igs_adam_step(_groups)  <- torch.optim.Adam(eps=1e-15) over the refine parameters
  *                              (igs/models/gaussian_model.py:348; infer_batch.py:323)
  *   igs_refine_loss         <- 0.8*L1 + 0.2*(1-SSIM) (infer_batch.py:301-305, igs/utils/loss_utils.py:16-62)
+ *   igs_depth_normal_loss   <- depth-normal consistency loss of frame-0 training (RADE/train.py:143-157,
+ *                              RADE/utils/graphics_utils.py:97-126)
  *   igs_activate_forward/backward <- exp / normalize / sigmoid activations (igs/models/gaussian_model.py:89-127)
  *   igs_densify_stats / igs_densify_gather <- densification statistics and the parameter / optimizer-state rebuild
  *                              of densify_and_prune (igs/models/gaussian_model.py:466-666,865-868)
@@ -57,7 +59,7 @@
 extern "C" {
 #endif
 
-#define IGS_RASTER_ABI_VERSION 4
+#define IGS_RASTER_ABI_VERSION 5
 
 typedef enum igs_status {
   IGS_OK = 0,
@@ -225,6 +227,19 @@ int igs_adam_step_groups(float* param, const float* grad, float* exp_avg, float*
 int igs_refine_loss(const float* pred, const float* gt, int V, int height, int width, float lambda_l1,
                     float grad_scale, const int* loss_rows, float* loss_sum, float* dL_dpred, igs_alloc_fn temp_alloc,
                     void* temp_user, void* stream);
+
+/* Depth-normal consistency loss of RaDe-GS frame-0 training, value and gradients in one launch (replaces
+ * RADE/train.py:143-157 with RADE/utils/graphics_utils.py:97-126 depths_double_to_points / point_double_to_normal):
+ *   *loss_sum = sum_v [ (1 - depth_ratio) * mean(1 - <normal_v, n(map0_v)>) + depth_ratio * mean(1 - <normal_v, n(map1_v)>) ]
+ * where n(.) is the normalised cross product of the central differences of the back-projected points (zero on the
+ * one-pixel border).  use_coord == 0: map0 / map1 are the expected / median DEPTH maps [V][H][W] and points are
+ * depth * K^-1 (x + 0.5, y + 0.5, 1) with fx = W / (2 tan_fovx); use_coord != 0: they are the expected / median COORD
+ * maps [V][3][H][W] (RADE/train.py:150-153).  dL_dmap0 / dL_dmap1 / dL_dnormal (same shapes as the inputs) receive
+ * grad_scale * d(*loss_sum)/d(.); *loss_sum (DEVICE float) is not scaled.  temp_alloc provides a few KB. */
+int igs_depth_normal_loss(int use_coord, const float* map0, const float* map1, const float* normal, int V, int height,
+                          int width, float tan_fovx, float tan_fovy, float depth_ratio, float grad_scale,
+                          float* loss_sum, float* dL_dmap0, float* dL_dmap1, float* dL_dnormal, igs_alloc_fn temp_alloc,
+                          void* temp_user, void* stream);
 
 /* Parameter activations of the refine loop and their chain rule (igs/models/gaussian_model.py:89-127, i.e.
  * RaDe-GS scene/gaussian_model.py setup_functions: scaling = exp, rotation = F.normalize (eps 1e-12),

@@ -35,7 +35,7 @@ def test_every_declared_symbol_is_exported(lib):
 
 
 def test_abi_version(lib):
-    assert lib.igs_abi_version() == 4
+    assert lib.igs_abi_version() == 5
 
 
 def test_null_arguments_are_rejected_without_touching_the_gpu(lib):
