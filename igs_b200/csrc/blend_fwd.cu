@@ -127,19 +127,22 @@ blend_fwd_kernel(BlendFwdParams p) {
         while (m) {
           const uint32_t kk = base + (__ffs(m) - 1);
           m &= m - 1;
-          if (done) continue;
+          // The tests of the reference (done / power > 0 / alpha < 1/255 / T underflow) are evaluated for every lane
+          // without branching — a warp instruction costs the same for 1 or 32 active lanes — and folded into ONE
+          // predicate, so the loop control stays warp-uniform and the body has a single divergent region.
           const uint32_t ak = rec_base + kk * 16;
           const float4 a = lds128<0>(ak);
           const float4 bq = lds128<BLEND_BATCH * 16>(ak);
           float dx, dy;
           unpack2(sub2(pack2(a.x, a.y), pix2), dx, dy);  // each rounded like fsub()
           const float power = splat_power(dx, dy, a.z, a.w, bq.x);
-          if (power > 0.0f) continue;
           const float alpha = fminf(0.99f, fmul(bq.y, expf(power)));
-          if (alpha < 1.0f / 255.0f) continue;
           float aT, test_T;
           unpack2(mul2(pack2(alpha, fsub(1.0f, alpha)), pack2(T, T)), aT, test_T);  // fmul(alpha, T), fmul(T, 1 - alpha)
-          if (test_T < 0.0001f) { done = 1; continue; }
+          const bool cand = (done == 0) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+          const bool term = cand && (test_T < 0.0001f);
+          if (term) done = 1;
+          if (!cand || term) continue;
           const float4 cq = lds128<BLEND_BATCH * 32>(ak);  // {blue, 1, position, tau}
           const uint32_t contributor = __float_as_uint(cq.z);
           const bool before_median = T > 0.5f;
