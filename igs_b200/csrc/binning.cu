@@ -129,25 +129,47 @@ radix_hist_kernel(const K* __restrict__ keys, size_t n, int shift, uint32_t mask
   for (int d = threadIdx.x; d < NB; d += IGS_SORT_THREADS) hist[(size_t)d * nblocks + blockIdx.x] = h[d];
 }
 
-// Each warp ranks a contiguous chunk of 512 keys in 16 rounds of 32 consecutive keys, so that the
-// rank order equals the index order (stability).  The kernel is latency bound (a serial chain of 16 match/rank
-// rounds per warp), so the per-thread state is kept small — digits are recomputed from the keys and the 16 ranks
-// (< 512) are packed two per register — to hold 4 CTAs per SM.
+// Each warp ranks a contiguous chunk of 512 keys in 16 rounds of 32 consecutive keys, so that the rank order equals
+// the index order (stability).  The ranked keys are then REORDERED IN SHARED MEMORY by digit and written out in index
+// order of that staging buffer, so every warp store covers contiguous runs of the destination: scattering 4-byte keys
+// straight from the ranking loop costs one L2 sector transaction per key and value (33 M instances x 2 per pass at C3
+// was the bound of the pass, ncu: 1.3 TB/s of algorithmic traffic), the staged write-out one per 32 bytes.
+template <typename K, int BITS>
+struct ScatterSmem {
+  static constexpr int NB = 1 << BITS;
+  static constexpr int WARPS = IGS_SORT_THREADS / 32;
+  static constexpr size_t whist_bytes = (size_t)WARPS * (NB + 1) * 4;
+  static constexpr size_t dig_bytes = (size_t)NB * 4 * 2;
+  static constexpr size_t key_off = (whist_bytes + dig_bytes + 64 + 15) & ~size_t(15);   // + wsum[8] (+ pad)
+  static constexpr size_t val_off = key_off + (size_t)IGS_SORT_TILE * sizeof(K);
+  static constexpr size_t bytes = val_off + (size_t)IGS_SORT_TILE * 4;
+};
+
 template <typename K, int BITS>
 __global__ void __launch_bounds__(IGS_SORT_THREADS, sizeof(K) == 4 ? 4 : 3)
 radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, K* __restrict__ keys_out,
                      uint32_t* __restrict__ vals_out, size_t n, int shift, uint32_t mask,
                      const uint32_t* __restrict__ hist_scanned, unsigned nblocks) {
+  using L = ScatterSmem<K, BITS>;
   constexpr int NB = 1 << BITS;
   constexpr int WARPS = IGS_SORT_THREADS / 32;
   constexpr int CHUNK = IGS_SORT_TILE / WARPS;      // 512 keys per warp
   constexpr int ROUNDS = CHUNK / 32;                // 16
-  __shared__ uint32_t whist[WARPS][NB + 1];
+  constexpr int PER = NB / IGS_SORT_THREADS;        // digits per thread in the block-level scan (1 or 2)
+  static_assert(NB % IGS_SORT_THREADS == 0, "digit count must be a multiple of the block size");
+  extern __shared__ __align__(16) unsigned char sort_smem[];
+  uint32_t (*whist)[NB + 1] = reinterpret_cast<uint32_t (*)[NB + 1]>(sort_smem);
+  uint32_t* dig_local = reinterpret_cast<uint32_t*>(sort_smem + L::whist_bytes);   // first staged slot of each digit
+  uint32_t* dig_global = dig_local + NB;                                             // destination of slot 0 of it
+  uint32_t* wsum = dig_global + NB;                                                  // [WARPS]
+  K* s_key = reinterpret_cast<K*>(sort_smem + L::key_off);
+  uint32_t* s_val = reinterpret_cast<uint32_t*>(sort_smem + L::val_off);
   const int w = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
   for (int i = threadIdx.x; i < WARPS * (NB + 1); i += IGS_SORT_THREADS) (&whist[0][0])[i] = 0;
 
-  const size_t wbase = (size_t)blockIdx.x * IGS_SORT_TILE + (size_t)w * CHUNK;
+  const size_t bbase = (size_t)blockIdx.x * IGS_SORT_TILE;
+  const size_t wbase = bbase + (size_t)w * CHUNK;
   K key[ROUNDS];
   uint32_t rnk2[ROUNDS / 2];
 #pragma unroll
@@ -175,15 +197,35 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
     __syncwarp();
   }
   __syncthreads();
-  // cross-warp exclusive scan per digit
-  for (uint32_t d = threadIdx.x; d < (uint32_t)NB; d += IGS_SORT_THREADS) {
-    uint32_t run = hist_scanned[(size_t)d * nblocks + blockIdx.x];
+  // per digit: exclusive scan over the warps (in place) and the block's count; then an exclusive scan of the counts
+  // over the digits gives each digit's first staged slot
+  uint32_t cnt[PER], tsum = 0;
+#pragma unroll
+  for (int q = 0; q < PER; q++) {
+    const uint32_t d = threadIdx.x * PER + q;
+    uint32_t run = 0;
 #pragma unroll
     for (int ww = 0; ww < WARPS; ww++) {
-      uint32_t c = whist[ww][d];
+      const uint32_t c = whist[ww][d];
       whist[ww][d] = run;
       run += c;
     }
+    cnt[q] = run;
+    tsum += run;
+  }
+  const uint32_t incl = warp_incl_scan(tsum);
+  if (lane == 31) wsum[w] = incl;
+  __syncthreads();
+  uint32_t start = incl - tsum;
+#pragma unroll
+  for (int ww = 0; ww < WARPS; ww++)
+    if (ww < w) start += wsum[ww];
+#pragma unroll
+  for (int q = 0; q < PER; q++) {
+    const uint32_t d = threadIdx.x * PER + q;
+    dig_local[d] = start;
+    dig_global[d] = hist_scanned[(size_t)d * nblocks + blockIdx.x] - start;   // modular: slot j of digit d -> dig_global[d] + j
+    start += cnt[q];
   }
   __syncthreads();
 #pragma unroll
@@ -191,10 +233,19 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
     const size_t i = wbase + (size_t)r * 32 + lane;
     if (i < n) {
       const uint32_t rk = (r & 1) ? (rnk2[r >> 1] >> 16) : (rnk2[r >> 1] & 0xffffu);
-      const uint32_t pos = myhist[digit_of<K>(key[r], shift, mask)] + rk;
-      keys_out[pos] = key[r];
-      vals_out[pos] = vals_in[i];
+      const uint32_t d = digit_of<K>(key[r], shift, mask);
+      const uint32_t slot = dig_local[d] + myhist[d] + rk;
+      s_key[slot] = key[r];
+      s_val[slot] = vals_in[i];
     }
+  }
+  __syncthreads();
+  const uint32_t nvalid = (uint32_t)(n - bbase < (size_t)IGS_SORT_TILE ? n - bbase : (size_t)IGS_SORT_TILE);
+  for (uint32_t j = threadIdx.x; j < nvalid; j += IGS_SORT_THREADS) {
+    const K k = s_key[j];
+    const uint32_t pos = dig_global[digit_of<K>(k, shift, mask)] + j;
+    keys_out[pos] = k;
+    vals_out[pos] = s_val[j];
   }
 }
 
@@ -203,6 +254,9 @@ static int radix_sort_passes(K* keys[2], uint32_t* vals[2], size_t n, int end_bi
   constexpr int NB = 1 << BITS;
   unsigned nb = (unsigned)sort_blocks(n);
   int cur = 0;
+  // > 48 KB of dynamic shared memory needs the opt-in; it is per device, so it is (cheaply) set on every sort
+  cudaFuncSetAttribute(radix_scatter_kernel<K, BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       (int)ScatterSmem<K, BITS>::bytes);
   for (int shift = 0; shift < end_bit; shift += BITS) {
     int bits = end_bit - shift < BITS ? end_bit - shift : BITS;
     uint32_t mask = (1u << bits) - 1u;
@@ -210,8 +264,8 @@ static int radix_sort_passes(K* keys[2], uint32_t* vals[2], size_t n, int end_bi
     radix_hist_kernel<K, BITS><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], n, shift, mask, hist, nb);
     // in-place exclusive scan over the bin-major histogram (its block sums live behind the histogram)
     launch_exclusive_scan(hist, hist, (size_t)NB * nb, hist + (size_t)NB * nb, nullptr, s);
-    radix_scatter_kernel<K, BITS><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n,
-                                                                  shift, mask, hist, nb);
+    radix_scatter_kernel<K, BITS><<<nb, IGS_SORT_THREADS, ScatterSmem<K, BITS>::bytes, s>>>(
+        keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift, mask, hist, nb);
     cur ^= 1;
   }
   return cur;
@@ -267,30 +321,61 @@ __device__ __forceinline__ void tile_rect(float px, float py, int radius, int ti
   y1 = min(row1, max(row0, (int)fmul(fadd(fadd(fadd(py, rf), 16.0f), -1.0f), 0.0625f)));
 }
 
+// One WARP per 32 consecutive depth-sorted Gaussians.  The warp's instances form one contiguous range of emission
+// slots; lanes walk that range slot by slot (fully coalesced 128-byte stores to the three arrays), finding each slot's
+// Gaussian with a 5-step binary search over the 32 lane-held offsets.  (One thread per Gaussian writing its own run of
+// slots — the reference's duplicateWithKeys loop — makes every store instruction touch up to 32 sectors.)
 __global__ void __launch_bounds__(256)
 emit_instances_kernel(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Camera* __restrict__ cams,
                       const uint32_t* __restrict__ sorted_gid,
                       const uint32_t* __restrict__ inst_off, const SplatHead* __restrict__ head,
                       const int* __restrict__ radii, uint32_t* __restrict__ tkey, uint32_t* __restrict__ tval,
                       uint32_t* __restrict__ inst_gid) {
-  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= VP) return;
-  uint32_t off = inst_off[i];
-  uint32_t n = inst_off[i + 1] - off;
-  if (n == 0) return;
-  uint32_t gid = sorted_gid[i];
-  uint32_t v = gid / P;
-  float4 h = head[gid].a;
-  int x0, y0, x1, y1;
-  tile_rect(h.x, h.y, radii[gid], tiles_x, cams[v].row0, cams[v].row1, x0, y0, x1, y1);
-  uint32_t tbase = v * (uint32_t)(tiles_x * tiles_y);
-  for (int y = y0; y < y1; y++)
-    for (int x = x0; x < x1; x++) {
-      tkey[off] = tbase + (uint32_t)(y * tiles_x + x);
-      tval[off] = off;
-      inst_gid[off] = gid;
-      off++;
+  const size_t wid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const uint32_t lane = lane_id();
+  const size_t i0 = wid * 32;
+  if (i0 >= VP) return;
+  const size_t i = i0 + lane;
+  const bool live = i < VP;
+  // lanes past the end take the end offset of the last Gaussian, so they own nothing
+  const size_t il = live ? i : VP;
+  const uint32_t off = inst_off[il];
+  const uint32_t n = live ? inst_off[i + 1] - off : 0u;
+  uint32_t gid = 0, xy = 0, width = 1, tbase = 0;
+  if (n != 0) {
+    gid = sorted_gid[i];
+    const uint32_t v = gid / P;
+    const float4 h = head[gid].a;
+    int x0, y0, x1, y1;
+    tile_rect(h.x, h.y, radii[gid], tiles_x, cams[v].row0, cams[v].row1, x0, y0, x1, y1);
+    xy = (uint32_t)x0 | ((uint32_t)y0 << 16);
+    width = (uint32_t)(x1 - x0);
+    tbase = v * (uint32_t)(tiles_x * tiles_y);
+  }
+  const uint32_t begin = __shfl_sync(0xffffffffu, off, 0);
+  const uint32_t end = __shfl_sync(0xffffffffu, off + n, 31);
+  for (uint32_t e0 = begin; e0 < end; e0 += 32) {     // warp-uniform trip count
+    const uint32_t e = e0 + lane;
+    // owner = last lane whose offset is <= e (Gaussians without instances share the offset of their successor)
+    uint32_t lo = 0;
+#pragma unroll
+    for (int step = 16; step > 0; step >>= 1) {
+      const uint32_t oc = __shfl_sync(0xffffffffu, off, lo + step);
+      if (oc <= e) lo += step;
     }
+    const uint32_t o_off = __shfl_sync(0xffffffffu, off, lo);
+    const uint32_t o_gid = __shfl_sync(0xffffffffu, gid, lo);
+    const uint32_t o_xy = __shfl_sync(0xffffffffu, xy, lo);
+    const uint32_t o_w = __shfl_sync(0xffffffffu, width, lo);
+    const uint32_t o_tb = __shfl_sync(0xffffffffu, tbase, lo);
+    if (e < end) {
+      const uint32_t local = e - o_off;
+      const uint32_t ry = local / o_w, rx = local - ry * o_w;
+      tkey[e] = o_tb + ((o_xy >> 16) + ry) * (uint32_t)tiles_x + (o_xy & 0xffffu) + rx;
+      tval[e] = e;
+      inst_gid[e] = o_gid;
+    }
+  }
 }
 
 void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Camera* cams,
@@ -298,7 +383,7 @@ void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, cons
                            const uint32_t* inst_off, const SplatHead* head, const int* radii, uint32_t* tkey,
                            uint32_t* tval, uint32_t* inst_gid, cudaStream_t s) {
   if (VP == 0) return;
-  unsigned nb = (unsigned)((VP + 255) / 256);
+  unsigned nb = (unsigned)((((VP + 31) / 32) * 32 + 255) / 256);   // one warp per 32 Gaussians, 8 warps per block
   count_launch();
   emit_instances_kernel<<<nb, 256, 0, s>>>(VP, P, tiles_x, tiles_y, cams, sorted_gid, inst_off, head, radii, tkey, tval,
                                            inst_gid);
