@@ -95,6 +95,19 @@ gather_bwd_kernel(GatherBwdParams p) {
   }
   const float dL_dopacity_in = s[9];
   dm2[0] = s[3]; dm2[1] = s[4]; dm2[2] = s[5];
+  // A visible Gaussian that contributed to no pixel (hidden behind opaque ones, or below 1/255 everywhere) has an
+  // all-zero record sum, and every output below is linear in it: its partial is exactly zero (the |grad| accumulator
+  // s[5] >= 0 is zero only if every value is).  Skipping the chain for them matters because this kernel is latency
+  // bound (146 registers).
+  {
+    float nz = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 25; i++) nz += fabsf(s[i]);
+    if (nz == 0.0f) {
+      part[0] = part[1] = part[2] = part[3] = make_float4(0, 0, 0, 0);
+      return;
+    }
+  }
 
   const Camera& cam = p.cams[v];
   const float* view = cam.view;
