@@ -372,8 +372,26 @@ __device__ __constant__ float bSH_C3[7] = {-0.5900435899266435f, 2.8906114426405
 template <int MAXC>
 __global__ void __launch_bounds__(128)
 finish_bwd_kernel(FinishBwdParams p) {
-  int g = blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= p.P) return;
+  // The SH coefficients of the block's 128 Gaussians are staged in shared memory with coalesced loads (and dL/dSH
+  // leaves the same way): read per thread straight from the [P][M][3] array, every scalar load touches 32 cache
+  // lines and the kernel sits at the L1 request limit (ncu: l1tex 84 % of peak, lg_throttle stalls).
+  constexpr int SROW = MAXC * 3 + 1;   // odd row stride: conflict-free per-thread rows
+  __shared__ float s_sh[MAXC > 1 ? 128 * SROW : 1];
+  const int g0 = blockIdx.x * blockDim.x;
+  const int g_raw = g0 + threadIdx.x;
+  const bool live = g_raw < p.P;
+  const int g = live ? g_raw : p.P - 1;
+  const int row = p.M * 3;             // floats per Gaussian in shs / dL_dsh
+  const bool staged = MAXC > 1 && p.shs != nullptr && row <= MAXC * 3;
+  if (staged) {
+    const int nrows = min(128, p.P - g0);
+    const float* src = p.shs + (size_t)g0 * row;
+    for (int f = threadIdx.x; f < nrows * row; f += 128) {
+      const int r = f / row;
+      s_sh[r * SROW + (f - r * row)] = src[f];
+    }
+    __syncthreads();
+  }
   float dmx = 0, dmy = 0, dmz = 0, dop = 0;
   float dcov[6] = {0, 0, 0, 0, 0, 0};
   float draw[3] = {0, 0, 0};
@@ -381,7 +399,7 @@ finish_bwd_kernel(FinishBwdParams p) {
 #pragma unroll
   for (int i = 0; i < MAXC * 3; i++) dsh[i] = 0.0f;
   const float mx = p.means3D[3 * g], my = p.means3D[3 * g + 1], mz = p.means3D[3 * g + 2];
-  const float* sh = p.shs ? p.shs + (size_t)g * p.M * 3 : nullptr;
+  const float* sh = p.shs ? (staged ? &s_sh[threadIdx.x * SROW] : p.shs + (size_t)g * p.M * 3) : nullptr;
 
   for (int v = 0; v < p.V; v++) {
     size_t gid = (size_t)v * p.P + g;
@@ -472,18 +490,32 @@ finish_bwd_kernel(FinishBwdParams p) {
     }
   }
 
+  if (p.dL_dsh != nullptr) {
+    if (staged) {   // through the staging tile: coalesced stores
+      __syncthreads();
+#pragma unroll
+      for (int i = 0; i < MAXC * 3; i++) s_sh[threadIdx.x * SROW + i] = dsh[i];
+      __syncthreads();
+      const int nrows = min(128, p.P - g0);
+      float* dst = p.dL_dsh + (size_t)g0 * row;
+      for (int f = threadIdx.x; f < nrows * row; f += 128) {
+        const int r = f / row;
+        dst[f] = s_sh[r * SROW + (f - r * row)];
+      }
+    } else if (live) {
+      float* o = p.dL_dsh + (size_t)g * p.M * 3;
+      for (int i = 0; i < p.M * 3; i++) o[i] = 0.0f;
+#pragma unroll
+      for (int i = 0; i < MAXC * 3; i++)
+        if (i < p.M * 3) o[i] = dsh[i];
+    }
+  }
+  if (!live) return;
   p.dL_dmeans3D[3 * g] = dmx; p.dL_dmeans3D[3 * g + 1] = dmy; p.dL_dmeans3D[3 * g + 2] = dmz;
 #pragma unroll
   for (int i = 0; i < 6; i++) p.dL_dcov3D[6 * g + i] = dcov[i];
   p.dL_dopacity[g] = dop;
   if (p.dL_dcolors) { p.dL_dcolors[3 * g] = draw[0]; p.dL_dcolors[3 * g + 1] = draw[1]; p.dL_dcolors[3 * g + 2] = draw[2]; }
-  if (p.dL_dsh != nullptr) {
-    float* o = p.dL_dsh + (size_t)g * p.M * 3;
-    for (int i = 0; i < p.M * 3; i++) o[i] = 0.0f;
-#pragma unroll
-    for (int i = 0; i < MAXC * 3; i++)
-      if (i < p.M * 3) o[i] = dsh[i];
-  }
   if (p.scales != nullptr && p.dL_dscales != nullptr) {
     // cov3D -> scale / quaternion (reference backward.cu:492-555); quaternion un-normalised
     const float4 q = reinterpret_cast<const float4*>(p.rotations)[g];
