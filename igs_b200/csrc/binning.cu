@@ -392,31 +392,49 @@ void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, cons
 // ---------------------------------------------------------------------------------------------
 // After sort B: tile ranges (reference identifyTileRanges) + sorted Gaussian-id list
 // ---------------------------------------------------------------------------------------------
+// Four consecutive instances per thread: 16-byte loads / stores of the sorted arrays and four independent gathers of
+// the Gaussian id in flight (one element per thread left the kernel latency bound on the dependent gather).
+__device__ __forceinline__ void mark_boundary(uint2* __restrict__ ranges, uint32_t tp, uint32_t t, uint32_t j) {
+  if (t != tp) {
+    ranges[tp].y = j;
+    ranges[t].x = j;
+  }
+}
+
 __global__ void __launch_bounds__(256)
 finalize_bins_kernel(uint32_t R, const uint32_t* __restrict__ tkey, const uint32_t* __restrict__ point_e,
                      const uint32_t* __restrict__ inst_gid, uint32_t* __restrict__ point_list,
                      uint2* __restrict__ ranges) {
-  uint32_t j = blockIdx.x * blockDim.x + threadIdx.x;
-  if (j >= R) return;
-  uint32_t t = tkey[j];
-  if (j == 0) {
-    ranges[t].x = 0;
+  const uint32_t j0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
+  if (j0 >= R) return;
+  if (j0 + 4 <= R) {
+    const uint4 t = *reinterpret_cast<const uint4*>(tkey + j0);
+    const uint4 e = *reinterpret_cast<const uint4*>(point_e + j0);
+    const uint4 g = make_uint4(inst_gid[e.x], inst_gid[e.y], inst_gid[e.z], inst_gid[e.w]);
+    if (j0 == 0) ranges[t.x].x = 0;
+    else mark_boundary(ranges, tkey[j0 - 1], t.x, j0);
+    mark_boundary(ranges, t.x, t.y, j0 + 1);
+    mark_boundary(ranges, t.y, t.z, j0 + 2);
+    mark_boundary(ranges, t.z, t.w, j0 + 3);
+    if (j0 + 4 == R) ranges[t.w].y = R;
+    *reinterpret_cast<uint4*>(point_list + j0) = g;
   } else {
-    uint32_t tp = tkey[j - 1];
-    if (t != tp) {
-      ranges[tp].y = j;
-      ranges[t].x = j;
+    for (uint32_t j = j0; j < R; j++) {
+      const uint32_t t = tkey[j];
+      if (j == 0) ranges[t].x = 0;
+      else mark_boundary(ranges, tkey[j - 1], t, j);
+      if (j == R - 1) ranges[t].y = R;
+      point_list[j] = inst_gid[point_e[j]];
     }
   }
-  if (j == R - 1) ranges[t].y = R;
-  point_list[j] = inst_gid[point_e[j]];
 }
 
 void launch_finalize_bins(uint32_t R, const uint32_t* tkey, const uint32_t* point_e, const uint32_t* inst_gid,
                           uint32_t* point_list, uint2* ranges, cudaStream_t s) {
   if (R == 0) return;
   count_launch();
-  finalize_bins_kernel<<<(R + 255) / 256, 256, 0, s>>>(R, tkey, point_e, inst_gid, point_list, ranges);
+  const uint32_t threads = (R + 3) / 4;
+  finalize_bins_kernel<<<(threads + 255) / 256, 256, 0, s>>>(R, tkey, point_e, inst_gid, point_list, ranges);
 }
 
 // Decode helper for tests: 64-bit reference-style keys in sorted order.

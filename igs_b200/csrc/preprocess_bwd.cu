@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(128, 4)
 gather_bwd_kernel(GatherBwdParams p) {
   // Threads are indexed by DEPTH-SORTED position: emission slots of neighbouring positions are adjacent in grec, so
   // the record reads of a warp fall into one contiguous region (the small per-Gaussian inputs become the gathers).
+  // (Indexing by (view, Gaussian) instead, with the record sum as the one gather, measured 3 % slower.)
   const size_t pos = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (pos >= (size_t)p.V * p.P) return;
   const size_t gid = p.sorted_gid[pos];
