@@ -251,7 +251,7 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   // ---- sort A: (view, depth) ----
   int cur;
   { StageScope st(IGS_STAGE_DEPTH_SORT, s);
-    cur = radix_sort_pairs<uint64_t>(G.skey, G.sval, VP, 32 + (V > 1 ? bits_for((uint64_t)V) : 0), G.hist, nullptr, s); }
+    cur = radix_sort_pairs<uint64_t>(G.skey, G.sval, VP, 31 + (V > 1 ? bits_for((uint64_t)V) : 0), G.hist, nullptr, s); }
   if (int e = debug_sync(dbg, s, "depth sort")) return e;
   const uint32_t* sorted_gid = G.sval[cur];
   uint32_t* d_total = G.scan_tmp + scan_blocks(VP + 1);

@@ -84,7 +84,7 @@ struct GeomBuf {
   int* radii;              // [V*P]
   uint32_t* tiles;         // [V*P] tiles touched
   uint8_t* clamped;        // [V*P] bit c: SH colour channel c clamped at 0
-  uint64_t* skey[2];       // [V*P] (view<<32 | depth bits), ping-pong
+  uint64_t* skey[2];       // [V*P] (view<<31 | 31 depth bits), ping-pong
   uint32_t* sval[2];       // [V*P] global Gaussian id (v*P+g), ping-pong
   uint32_t* rank;          // [V*P] gid -> position in depth-sorted order
   uint32_t* inst_off;      // [V*P+1] exclusive scan of tiles in depth-sorted order

@@ -352,7 +352,9 @@ project_kernel(ProjectParams p, const Camera* __restrict__ cams, const float* __
   radii_geom[gid] = radius_i;
   if (radii_out != nullptr) radii_out[gid] = radius_i;
   tiles_out[gid] = ntiles;
-  skey[gid] = ((uint64_t)v << 32) | depth_bits;
+  // depth bits of a visible Gaussian are those of a float > 0.2 (sign bit clear); invisible ones sort last with the
+  // all-ones 31-bit pattern.  31 + bits(V) key bits: 36 at V = 20, i.e. four 9-bit radix passes instead of five.
+  skey[gid] = ((uint64_t)v << 31) | (uint64_t)(depth_bits & 0x7FFFFFFFu);
   sval[gid] = (uint32_t)gid;
 }
 
