@@ -450,6 +450,20 @@ def main():
         allr = [per_rank]
     per_rank = [{"views": round(float(t[0]), 2), "R": int(t[1]), "stage_ms": round(float(t[2]), 3)} for t in allr]
 
+    # ---- (1b) the same step without the geometry maps nobody reads (extra; NOT the headline) ----
+    # The refine loop's loss reads the colour map only (infer_batch.py:300-305); the reference still renders
+    # coord / depth / normal because its rasterizer is called with require_coord = require_depth = True.  Inside the
+    # fused native step those maps never leave the call, so eliding them changes no result (loss, gradients and radii
+    # are bit-identical: tests/test_refine_gpu.py); `value` keeps them, this key shows the step without them.
+    ms_lean = None
+    if Vl:
+        st_lean = st._replace(require_coord=False, require_depth=False)
+
+        def step_lean():
+            state.flat.copy_(snapshot)
+            return refine.refine_iteration(state, st_lean, gt_local, V, group=group, loss_impl=loss_impl)
+        ms_lean, _ = timed(step_lean, args.steps, 3)
+
     # ---- (2) forward-only throughput ----
     def fwd_only():
         with torch.no_grad():
@@ -592,7 +606,7 @@ def main():
         "ms_per_step": ms_step, "higher_is_better": False, "scaling": "strong", "vs_baseline": None, "dtype": "f32",
         "data": "synthetic", "config": workload_config(args, cfg), "e2e": e2e, "gpu_launches": int(launches),
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
-        "fwd_mpix_s": fwd_mpix, "fwd_ms": ms_fwd, "loss": loss_val, "loss_impl": loss_impl,
+        "value_without_unused_geometry_maps": ms_lean, "fwd_mpix_s": fwd_mpix, "fwd_ms": ms_fwd, "loss": loss_val, "loss_impl": loss_impl,
         "num_rendered_rank0": int(R_local), "allreduce_ms": allreduce_ms,
         "allreduce_bytes": int(state.grad.numel() * 4), "per_rank": per_rank, "view_assignment": assignment, "step_ms": step_stats.get("resident"), "first_attempt": first_attempt, "work": work, "stages": stage_report, "ref_cuda": ref_cuda,
     }

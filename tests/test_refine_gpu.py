@@ -248,3 +248,18 @@ def test_band_sharded_step_equals_single_rank_step(cuda_dev, native, world):
         a, b, _k = state.slices[name]
         assert float((total[a:b] - g_all[a:b]).abs().max()) <= 2e-4 * float(g_all[a:b].abs().max()), name
     assert rendered < 1.35 * r_all.num_rendered   # the halo rows are the only duplicated work
+
+
+def test_step_without_geometry_maps_is_bit_identical(cuda_dev, native):
+    """require_coord = require_depth = False inside the fused step (the maps the refine loss never reads are not
+    rendered): loss, packed gradients, radii, instance count and screen-space gradients are the same bits."""
+    from igs_b200 import refine
+    P, V, W, H = 15000, 3, 176, 120
+    state, st = _state_and_settings(cuda_dev, P, V, W, H)
+    gt = torch.rand(V, 3, H, W, generator=torch.Generator().manual_seed(31)).to(cuda_dev)
+    a = refine.refine_iteration(state, st, gt, V, do_step=False)
+    g_a = state.grad.clone()
+    state.grad.fill_(float("nan"))
+    b = refine.refine_iteration(state, st._replace(require_coord=False, require_depth=False), gt, V, do_step=False)
+    assert torch.equal(state.grad, g_a) and float(a.loss) == float(b.loss)
+    assert a.num_rendered == b.num_rendered and torch.equal(a.radii, b.radii) and torch.equal(a.grad_means2D, b.grad_means2D)
