@@ -268,9 +268,17 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   write_header_kernel<<<1, 1, 0, s>>>(G.hdr, hv, d_total);
 
   // ---- the one host sync: instance count (reference rasterizer_impl.cu:354) ----
-  uint32_t R = 0;
-  IGS_CUDA_CHECK(cudaMemcpyAsync(&R, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+  // read through a pinned word (one per host thread): a copy into pageable memory is staged by the driver
+  static thread_local uint32_t* pinned_R = nullptr;
+  if (pinned_R == nullptr && cudaHostAlloc(reinterpret_cast<void**>(&pinned_R), 64, cudaHostAllocPortable) != cudaSuccess) {
+    pinned_R = nullptr;
+    (void)cudaGetLastError();
+  }
+  uint32_t R_pageable = 0;
+  uint32_t* R_dst = pinned_R ? pinned_R : &R_pageable;
+  IGS_CUDA_CHECK(cudaMemcpyAsync(R_dst, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
   IGS_CUDA_CHECK(cudaStreamSynchronize(s));
+  const uint32_t R = *R_dst;
   if (R > 0x7FFFFFFFu) { set_error("too many instances: %u", R); return IGS_ERR_UNSUPPORTED; }
 
   BinBuf bsz = carve_bin(nullptr, R);
