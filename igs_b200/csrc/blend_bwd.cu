@@ -58,7 +58,8 @@ __global__ void __launch_bounds__(256, MINB)
 blend_bwd_kernel(BlendBwdParams p) {
   constexpr int NS = GEOGRAD ? 32 : 16;         // floats per gradient record in global memory
   constexpr int NV = GEOGRAD ? 25 : 10;         // values actually produced per pair
-  constexpr int AS = GEOGRAD ? 25 : 11;         // accumulator stride per batch slot (colour-only: + one sink word)
+  constexpr int AS = GEOGRAD ? 25 : 12;         // accumulator stride per batch slot (colour-only: 10 values, a sink word,
+                                                // one pad word: 16-byte rows for the vectorised record write-out)
   constexpr int BATCH = bwd_batch(GEOGRAD, MINB);
   constexpr bool GEO = GEOGRAD && (COORD || DEPTH || NORMAL);
   // survivors: [0,B) head.a {x, y, conic.x, conic.y}; [B,2B) head.b {conic.z, opacity, r, g};
@@ -72,7 +73,7 @@ blend_bwd_kernel(BlendBwdParams p) {
   __shared__ uint32_t s_red[8];
   // per-warp private gradient accumulators [8][BATCH][NV]: no shared-memory atomics (float atomics on shared
   // memory are CAS loops), summed over the 8 warps when the batch's records are written
-  extern __shared__ float s_acc[];
+  extern __shared__ __align__(16) float s_acc[];
   // colour-only path: per-warp [10][36] transpose staging for the cross-pixel reduction (columns 32..35 stay zero)
   __shared__ __align__(16) float s_stage[GEOGRAD ? 4 : 8 * 10 * 36];
 
@@ -386,18 +387,37 @@ blend_bwd_kernel(BlendBwdParams p) {
     }
     __syncthreads();
     // ---- 3. one dense record per instance of this batch: sum (and clear) the 8 warps' accumulators ----
-    for (uint32_t f = threadIdx.x; f < nb * NS; f += 256) {
-      const uint32_t sl = f / NS, q = f % NS;
-      float sum = 0.0f;
-      if (q < NV) {
+    if constexpr (GEOGRAD) {
+      for (uint32_t f = threadIdx.x; f < nb * NS; f += 256) {
+        const uint32_t sl = f / NS, q = f % NS;
+        float sum = 0.0f;
+        if (q < NV) {
 #pragma unroll
-        for (int ww = 0; ww < 8; ww++) {
-          float* pa = s_acc + ((size_t)ww * BATCH + sl) * AS + q;
-          sum += *pa;
-          *pa = 0.0f;
+          for (int ww = 0; ww < 8; ww++) {
+            float* pa = s_acc + ((size_t)ww * BATCH + sl) * AS + q;
+            sum += *pa;
+            *pa = 0.0f;
+          }
         }
+        p.grec[(size_t)s_e[sl] * NS + q] = sum;
       }
-      p.grec[(size_t)s_e[sl] * NS + q] = sum;
+    } else {
+      // 16 bytes of a record per thread: three quarters come from the accumulators (values 0-9; words 10, 11 are the
+      // sink / pad and are ignored downstream), the fourth is zero so that every 32-byte sector is written whole
+      for (uint32_t f = threadIdx.x; f < nb * 4; f += 256) {
+        const uint32_t sl = f >> 2, q4 = f & 3;
+        float4 sum = make_float4(0, 0, 0, 0);
+        if (q4 < 3) {
+#pragma unroll
+          for (int ww = 0; ww < 8; ww++) {
+            float4* pa = reinterpret_cast<float4*>(s_acc + ((size_t)ww * BATCH + sl) * AS) + q4;
+            const float4 x = *pa;
+            sum.x += x.x; sum.y += x.y; sum.z += x.z; sum.w += x.w;
+            *pa = make_float4(0, 0, 0, 0);
+          }
+        }
+        reinterpret_cast<float4*>(p.grec + (size_t)s_e[sl] * NS)[q4] = sum;
+      }
     }
     __syncthreads();
     hi = lo;
@@ -408,7 +428,7 @@ int blend_bwd_record_floats(bool geograd) { return geograd ? 32 : 16; }
 
 template <bool C, bool D, bool N, bool G, int MINB>
 static void launch_one(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
-  constexpr int bytes = 8 * bwd_batch(G, MINB) * (G ? 25 : 11) * 4;  // per-warp accumulators (dynamic shared memory)
+  constexpr int bytes = 8 * bwd_batch(G, MINB) * (G ? 25 : 12) * 4;  // per-warp accumulators (dynamic shared memory)
   // > 48 KB of dynamic shared memory needs the opt-in; it is per device, so it is (cheaply) set on every launch
   cudaFuncSetAttribute(blend_bwd_kernel<C, D, N, G, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
   blend_bwd_kernel<C, D, N, G, MINB><<<nblocks, 256, bytes, s>>>(p);
