@@ -107,3 +107,41 @@ def test_forward_backward_through_ctypes(cuda_dev, native):
     b.binning_buffer, b.image_buffer = al(img), al(binning)   # swapped
     assert lib.igs_rasterize_backward(C.byref(b), a_tmp, None, C.c_void_p(stream)) == -1
     assert b"does not belong" in lib.igs_last_error()
+
+
+def test_depth_normal_loss_through_ctypes(cuda_dev, native):
+    """igs_depth_normal_loss with raw device pointers against the golden produced by the reference's own helpers."""
+    import math
+    lib = C.CDLL(str(ROOT / "igs_b200" / "lib" / "libigs_raster.so"))
+    lib.igs_last_error.restype = C.c_char_p
+    g = dict(np.load(cases.GOLDEN_DIR / "refmath_frame0.npz"))
+    dev = cuda_dev
+    d1 = torch.from_numpy(g["a_depth1"]).to(dev).contiguous()
+    d2 = torch.from_numpy(g["a_depth2"]).to(dev).contiguous()
+    nrm = torch.from_numpy(g["a_normal"]).to(dev).contiguous()
+    H, W = nrm.shape[1:]
+    tfx, tfy = (math.tan(float(f) / 2) for f in g["a_fov"])
+    loss = torch.zeros(1, device=dev)
+    g1, g2, gn = torch.empty_like(d1), torch.empty_like(d2), torch.empty_like(nrm)
+    keep = {}
+
+    def alloc(user, nbytes):
+        keep["t"] = torch.empty(int(nbytes) + 256, dtype=torch.uint8, device=dev)
+        return (keep["t"].data_ptr() + 255) & ~255
+    ptr = lambda t: C.c_void_p(t.data_ptr())  # noqa: E731
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    rc = lib.igs_depth_normal_loss(C.c_int(0), ptr(d1), ptr(d2), ptr(nrm), C.c_int(1), C.c_int(H), C.c_int(W), C.c_float(tfx),
+                                   C.c_float(tfy), C.c_float(0.6), C.c_float(1.0), ptr(loss), ptr(g1), ptr(g2), ptr(gn),
+                                   ALLOC(alloc), None, stream)
+    assert rc == 0, lib.igs_last_error()
+    torch.cuda.synchronize()
+    assert abs(float(loss) - float(g["a_loss"])) <= 2e-6
+    for got, k in ((g1, "a_d_depth1"), (g2, "a_d_depth2"), (gn, "a_d_normal")):
+        assert np.abs(got.cpu().numpy() - g[k]).max() <= 1e-3 * np.abs(g[k]).max(), k
+    # argument checks: no allocator / null pointers -> IGS_ERR_INVALID, nothing launched
+    assert lib.igs_depth_normal_loss(C.c_int(0), ptr(d1), ptr(d2), ptr(nrm), C.c_int(1), C.c_int(H), C.c_int(W), C.c_float(tfx),
+                                     C.c_float(tfy), C.c_float(0.6), C.c_float(1.0), ptr(loss), ptr(g1), ptr(g2), ptr(gn),
+                                     None, None, stream) == -1
+    assert lib.igs_depth_normal_loss(C.c_int(0), None, ptr(d2), ptr(nrm), C.c_int(1), C.c_int(H), C.c_int(W), C.c_float(tfx),
+                                     C.c_float(tfy), C.c_float(0.6), C.c_float(1.0), ptr(loss), ptr(g1), ptr(g2), ptr(gn),
+                                     ALLOC(alloc), None, stream) == -1
