@@ -60,7 +60,10 @@ sum_records_kernel(size_t VP, const uint32_t* __restrict__ inst_off, const float
   reinterpret_cast<float4*>(sums)[pos * PARTS + part] = acc;
 }
 
-__global__ void __launch_bounds__(128, 4)
+#ifndef IGS_GATHER_MINB
+#define IGS_GATHER_MINB 4
+#endif
+__global__ void __launch_bounds__(128, IGS_GATHER_MINB)
 gather_bwd_kernel(GatherBwdParams p) {
   // Threads are indexed by DEPTH-SORTED position: emission slots of neighbouring positions are adjacent in grec, so
   // the record reads of a warp fall into one contiguous region (the small per-Gaussian inputs become the gathers).
