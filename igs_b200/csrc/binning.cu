@@ -12,6 +12,8 @@
 // (SURVEY T8/T9); tests compare the decoded 64-bit keys / point_list / ranges bit-for-bit.
 #include "common.cuh"
 #include "kernels.cuh"
+#include <cooperative_groups.h>
+#include <cstdlib>
 
 namespace igs {
 
@@ -43,10 +45,9 @@ __device__ __forceinline__ uint32_t block_reduce_sum(uint32_t v, uint32_t* smem 
   return t;
 }
 
-__global__ void __launch_bounds__(SCAN_THREADS)
-scan_block_sums_kernel(const uint32_t* __restrict__ in, size_t n, uint32_t* __restrict__ sums) {
-  __shared__ uint32_t sm[8];
-  size_t base = (size_t)blockIdx.x * SCAN_TILE;
+__device__ __forceinline__ void scan_block_sums_body(const uint32_t* __restrict__ in, size_t n, uint32_t* __restrict__ sums,
+                                                     unsigned blk, uint32_t* sm /*>= 8 words*/) {
+  size_t base = (size_t)blk * SCAN_TILE;
   uint32_t s = 0;
 #pragma unroll
   for (int k = 0; k < SCAN_ITEMS; k++) {
@@ -54,21 +55,24 @@ scan_block_sums_kernel(const uint32_t* __restrict__ in, size_t n, uint32_t* __re
     if (i < n) s += in[i];
   }
   s = block_reduce_sum(s, sm);
-  if (threadIdx.x == 0) sums[blockIdx.x] = s;
+  if (threadIdx.x == 0) sums[blk] = s;
 }
 
-// out may alias in.  If total != nullptr the grand total is written by the last block.
 __global__ void __launch_bounds__(SCAN_THREADS)
-scan_apply_kernel(const uint32_t* in, size_t n, const uint32_t* __restrict__ sums, uint32_t* out,
-                  uint32_t* __restrict__ total) {
+scan_block_sums_kernel(const uint32_t* __restrict__ in, size_t n, uint32_t* __restrict__ sums) {
   __shared__ uint32_t sm[8];
-  __shared__ uint32_t wsum[SCAN_THREADS / 32];
+  scan_block_sums_body(in, n, sums, blockIdx.x, sm);
+}
+
+__device__ __forceinline__ void scan_apply_body(const uint32_t* in, size_t n, const uint32_t* __restrict__ sums, uint32_t* out,
+                                                uint32_t* __restrict__ total, unsigned blk, unsigned nblk, uint32_t* sm /*>= 8*/,
+                                                uint32_t* wsum /*>= 8*/) {
   // base = sum of all previous block sums
   uint32_t b = 0;
-  for (uint32_t j = threadIdx.x; j < blockIdx.x; j += SCAN_THREADS) b += sums[j];
+  for (uint32_t j = threadIdx.x; j < blk; j += SCAN_THREADS) b += sums[j];
   b = block_reduce_sum(b, sm);
 
-  size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+  size_t base = (size_t)blk * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
   uint32_t v[SCAN_ITEMS];
   uint32_t tsum = 0;
 #pragma unroll
@@ -78,6 +82,7 @@ scan_apply_kernel(const uint32_t* in, size_t n, const uint32_t* __restrict__ sum
     tsum += v[k];
   }
   uint32_t incl = warp_incl_scan(tsum);
+  __syncthreads();   // wsum may still be read by the previous tile of a persistent caller
   if (lane_id() == 31) wsum[threadIdx.x >> 5] = incl;
   __syncthreads();
   uint32_t woff = 0;
@@ -91,7 +96,16 @@ scan_apply_kernel(const uint32_t* in, size_t n, const uint32_t* __restrict__ sum
     if (i < n) out[i] = run;
     run += v[k];
   }
-  if (total != nullptr && blockIdx.x == gridDim.x - 1 && threadIdx.x == SCAN_THREADS - 1) *total = run;
+  if (total != nullptr && blk == nblk - 1 && threadIdx.x == SCAN_THREADS - 1) *total = run;
+}
+
+// out may alias in.  If total != nullptr the grand total is written by the last block.
+__global__ void __launch_bounds__(SCAN_THREADS)
+scan_apply_kernel(const uint32_t* in, size_t n, const uint32_t* __restrict__ sums, uint32_t* out,
+                  uint32_t* __restrict__ total) {
+  __shared__ uint32_t sm[8];
+  __shared__ uint32_t wsum[SCAN_THREADS / 32];
+  scan_apply_body(in, n, sums, out, total, blockIdx.x, gridDim.x, sm, wsum);
 }
 
 void launch_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint32_t* block_sums,
@@ -112,21 +126,28 @@ __device__ __forceinline__ uint32_t digit_of(K key, int shift, uint32_t mask) {
 }
 
 template <typename K, int BITS>
-__global__ void __launch_bounds__(IGS_SORT_THREADS)
-radix_hist_kernel(const K* __restrict__ keys, size_t n, int shift, uint32_t mask, uint32_t* __restrict__ hist,
-                  unsigned nblocks) {
+__device__ __forceinline__ void radix_hist_body(const K* __restrict__ keys, size_t n, int shift, uint32_t mask,
+                                                uint32_t* __restrict__ hist, unsigned nblocks, unsigned tile, uint32_t* h) {
   constexpr int NB = 1 << BITS;
-  __shared__ uint32_t h[NB];
+  __syncthreads();   // h may still be read by the previous tile of a persistent caller
   for (int d = threadIdx.x; d < NB; d += IGS_SORT_THREADS) h[d] = 0;
   __syncthreads();
-  size_t base = (size_t)blockIdx.x * IGS_SORT_TILE;
+  size_t base = (size_t)tile * IGS_SORT_TILE;
 #pragma unroll
   for (int k = 0; k < IGS_SORT_ITEMS; k++) {
     size_t i = base + (size_t)k * IGS_SORT_THREADS + threadIdx.x;
     if (i < n) atomicAdd(&h[digit_of<K>(keys[i], shift, mask)], 1u);
   }
   __syncthreads();
-  for (int d = threadIdx.x; d < NB; d += IGS_SORT_THREADS) hist[(size_t)d * nblocks + blockIdx.x] = h[d];
+  for (int d = threadIdx.x; d < NB; d += IGS_SORT_THREADS) hist[(size_t)d * nblocks + tile] = h[d];
+}
+
+template <typename K, int BITS>
+__global__ void __launch_bounds__(IGS_SORT_THREADS)
+radix_hist_kernel(const K* __restrict__ keys, size_t n, int shift, uint32_t mask, uint32_t* __restrict__ hist,
+                  unsigned nblocks) {
+  __shared__ uint32_t h[1 << BITS];
+  radix_hist_body<K, BITS>(keys, n, shift, mask, hist, nblocks, blockIdx.x, h);
 }
 
 // Each warp ranks a contiguous chunk of 512 keys in 16 rounds of 32 consecutive keys, so that the rank order equals
@@ -146,10 +167,10 @@ struct ScatterSmem {
 };
 
 template <typename K, int BITS>
-__global__ void __launch_bounds__(IGS_SORT_THREADS, sizeof(K) == 4 ? 4 : 3)
-radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, K* __restrict__ keys_out,
-                     uint32_t* __restrict__ vals_out, size_t n, int shift, uint32_t mask,
-                     const uint32_t* __restrict__ hist_scanned, unsigned nblocks) {
+__device__ __forceinline__ void radix_scatter_body(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in,
+                                                   K* __restrict__ keys_out, uint32_t* __restrict__ vals_out, size_t n, int shift,
+                                                   uint32_t mask, const uint32_t* __restrict__ hist_scanned, unsigned nblocks,
+                                                   unsigned tile, unsigned char* sort_smem) {
   using L = ScatterSmem<K, BITS>;
   constexpr int NB = 1 << BITS;
   constexpr int WARPS = IGS_SORT_THREADS / 32;
@@ -157,7 +178,6 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
   constexpr int ROUNDS = CHUNK / 32;                // 16
   constexpr int PER = NB / IGS_SORT_THREADS;        // digits per thread in the block-level scan (1 or 2)
   static_assert(NB % IGS_SORT_THREADS == 0, "digit count must be a multiple of the block size");
-  extern __shared__ __align__(16) unsigned char sort_smem[];
   uint32_t (*whist)[NB + 1] = reinterpret_cast<uint32_t (*)[NB + 1]>(sort_smem);
   uint32_t* dig_local = reinterpret_cast<uint32_t*>(sort_smem + L::whist_bytes);   // first staged slot of each digit
   uint32_t* dig_global = dig_local + NB;                                             // destination of slot 0 of it
@@ -166,9 +186,10 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
   uint32_t* s_val = reinterpret_cast<uint32_t*>(sort_smem + L::val_off);
   const int w = threadIdx.x >> 5;
   const uint32_t lane = lane_id();
+  __syncthreads();   // the staging buffers may still be read by the previous tile of a persistent caller
   for (int i = threadIdx.x; i < WARPS * (NB + 1); i += IGS_SORT_THREADS) (&whist[0][0])[i] = 0;
 
-  const size_t bbase = (size_t)blockIdx.x * IGS_SORT_TILE;
+  const size_t bbase = (size_t)tile * IGS_SORT_TILE;
   const size_t wbase = bbase + (size_t)w * CHUNK;
   K key[ROUNDS];
   uint32_t rnk2[ROUNDS / 2];
@@ -224,7 +245,7 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
   for (int q = 0; q < PER; q++) {
     const uint32_t d = threadIdx.x * PER + q;
     dig_local[d] = start;
-    dig_global[d] = hist_scanned[(size_t)d * nblocks + blockIdx.x] - start;   // modular: slot j of digit d -> dig_global[d] + j
+    dig_global[d] = hist_scanned[(size_t)d * nblocks + tile] - start;   // modular: slot j of digit d -> dig_global[d] + j
     start += cnt[q];
   }
   __syncthreads();
@@ -250,9 +271,90 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
 }
 
 template <typename K, int BITS>
+__global__ void __launch_bounds__(IGS_SORT_THREADS, sizeof(K) == 4 ? 4 : 3)
+radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, K* __restrict__ keys_out,
+                     uint32_t* __restrict__ vals_out, size_t n, int shift, uint32_t mask,
+                     const uint32_t* __restrict__ hist_scanned, unsigned nblocks) {
+  extern __shared__ __align__(16) unsigned char sort_smem[];
+  radix_scatter_body<K, BITS>(keys_in, vals_in, keys_out, vals_out, n, shift, mask, hist_scanned, nblocks, blockIdx.x, sort_smem);
+}
+
+// The whole sort in ONE cooperative launch: persistent CTAs loop over the tiles of each phase (histogram, the two scan
+// phases, scatter) with a grid barrier between phases, for every digit pass.  A multi-launch sort is 4 launches per
+// pass — 24 launches per rasterizer forward for the two sorts — and at small sizes (one 512x512 or 1280x720 view, or
+// the 2.5 views a rank renders at N = 8) those launches, not the kernels, were the cost of binning.
+template <typename K, int BITS>
+__global__ void __launch_bounds__(IGS_SORT_THREADS, sizeof(K) == 4 ? 4 : 3)
+radix_sort_coop_kernel(K* k0, K* k1, uint32_t* v0, uint32_t* v1, size_t n, int end_bit, uint32_t* hist, unsigned ntiles) {
+  constexpr int NB = 1 << BITS;
+  extern __shared__ __align__(16) unsigned char sort_smem[];
+  uint32_t* sm32 = reinterpret_cast<uint32_t*>(sort_smem);
+  cooperative_groups::grid_group grid = cooperative_groups::this_grid();
+  const size_t entries = (size_t)NB * ntiles;
+  const unsigned nchunks = (unsigned)scan_blocks(entries);
+  uint32_t* sums = hist + entries;
+  K* kin = k0; K* kout = k1;
+  uint32_t* vin = v0; uint32_t* vout = v1;
+  for (int shift = 0; shift < end_bit; shift += BITS) {
+    const int bits = end_bit - shift < BITS ? end_bit - shift : BITS;
+    const uint32_t mask = (1u << bits) - 1u;
+    for (unsigned t = blockIdx.x; t < ntiles; t += gridDim.x) radix_hist_body<K, BITS>(kin, n, shift, mask, hist, ntiles, t, sm32);
+    grid.sync();
+    for (unsigned c = blockIdx.x; c < nchunks; c += gridDim.x) scan_block_sums_body(hist, entries, sums, c, sm32);
+    grid.sync();
+    for (unsigned c = blockIdx.x; c < nchunks; c += gridDim.x)
+      scan_apply_body(hist, entries, sums, hist, nullptr, c, nchunks, sm32, sm32 + 8);
+    grid.sync();
+    for (unsigned t = blockIdx.x; t < ntiles; t += gridDim.x)
+      radix_scatter_body<K, BITS>(kin, vin, kout, vout, n, shift, mask, hist, ntiles, t, sort_smem);
+    grid.sync();
+    K* tk = kin; kin = kout; kout = tk;
+    uint32_t* tv = vin; vin = vout; vout = tv;
+  }
+}
+
+template <typename K, int BITS>
+static int coop_capacity() {   // co-resident CTAs of the cooperative sort kernel on the current device (0: unsupported)
+  static thread_local int cached_dev = -1, cached = 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 0;
+  if (dev == cached_dev) return cached;
+  int coop = 0, sms = 0, per_sm = 0;
+  cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  cudaFuncSetAttribute(radix_sort_coop_kernel<K, BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                       (int)ScatterSmem<K, BITS>::bytes);
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, radix_sort_coop_kernel<K, BITS>, IGS_SORT_THREADS,
+                                                    ScatterSmem<K, BITS>::bytes) != cudaSuccess) per_sm = 0;
+  (void)cudaGetLastError();
+  cached_dev = dev;
+  cached = coop ? per_sm * sms : 0;
+  return cached;
+}
+
+template <typename K, int BITS>
 static int radix_sort_passes(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint32_t* hist, cudaStream_t s) {
   constexpr int NB = 1 << BITS;
   unsigned nb = (unsigned)sort_blocks(n);
+  const int passes = (end_bit + BITS - 1) / BITS;
+  static const bool coop_off = [] { const char* e = getenv("IGS_SORT_COOP"); return e && atoi(e) == 0; }();
+  const int cap = coop_off ? 0 : coop_capacity<K, BITS>();
+  // Only when every tile gets its own resident CTA: with more tiles than that the persistent loop measured slower
+  // than separate launches (C3, 20 views: depth sort 0.40 -> 0.47 ms, tile sort 0.70 -> 0.88 ms), and at that size the
+  // launches are not the cost.
+  if (cap > 0 && passes > 0 && nb <= (unsigned)cap) {
+    unsigned grid = nb;
+    K* k0 = keys[0]; K* k1 = keys[1];
+    uint32_t* v0 = vals[0]; uint32_t* v1 = vals[1];
+    void* args[] = {&k0, &k1, &v0, &v1, &n, &end_bit, &hist, &nb};
+    cudaError_t e = cudaLaunchCooperativeKernel((const void*)radix_sort_coop_kernel<K, BITS>, dim3(grid), dim3(IGS_SORT_THREADS),
+                                                args, ScatterSmem<K, BITS>::bytes, s);
+    if (e == cudaSuccess) {
+      count_launch(1);
+      return passes & 1;
+    }
+    (void)cudaGetLastError();   // fall through to the multi-launch sort
+  }
   int cur = 0;
   // > 48 KB of dynamic shared memory needs the opt-in; it is per device, so it is (cheaply) set on every sort
   cudaFuncSetAttribute(radix_scatter_kernel<K, BITS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
