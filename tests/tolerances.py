@@ -1,11 +1,22 @@
 """Parity tolerances (BASELINE.json north_star): bit-exact integer/index outputs, max-abs 1e-4 on the
-seven fp32 maps, 1e-3 relative on gradients.  "Relative" is max|a-b| / max|ref| per gradient tensor:
-reference gradients are sums of float atomics in arbitrary order, so element-wise relative
-error is not defined by the reference itself."""
+seven fp32 maps, 1e-3 relative on gradients.  Reference gradients are sums of float atomics in arbitrary order
+(SURVEY T24), so element-wise relative error is not defined by the reference itself; two per-tensor criteria are
+used together:
+  * GRAD_RTOL  max|a-b| / max|ref|      (no element may be off by more than 1e-3 of the tensor's scale), and
+  * GRAD_RL2   ||a-b||_2 / ||ref||_2    (the error ENERGY is bounded too: a max-normalised bar alone lets every
+               element 100x smaller than the maximum be 10 % wrong).  Against the mean of three runs of the reference
+               build the observed values are 2e-7 .. 3e-5 (1.8e-4 for rotations before the conditioning mask)."""
 import numpy as np
 
 MAP_ATOL = 1e-4
 GRAD_RTOL = 1e-3
+GRAD_RL2 = 1e-4
+
+
+def grad_rel_l2(a, ref):
+    a = np.asarray(a, np.float64).reshape(np.shape(ref))
+    ref = np.asarray(ref, np.float64)
+    return float(np.linalg.norm(a - ref) / (np.linalg.norm(ref) + 1e-30))
 
 
 def grad_err(a, ref):
