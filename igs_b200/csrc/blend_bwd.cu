@@ -424,6 +424,331 @@ blend_bwd_kernel(BlendBwdParams p) {
   }
 }
 
+
+// ---------------------------------------------------------------------------------------------
+// Colour-only backward, two-pass form (the refine loop's kernel; selected by launch_blend_bwd).
+//
+// The kernel above reduces every (8x4 block, instance) pair's ten partial derivatives across the 32 pixels of
+// the warp right away: 10 STS + 3 LDS.128 + a read-modify-write per pair, which put it on the shared-memory pipe
+// (ncu r01: l1tex 87 %, 27 shared wavefronts and 31 of 113 instructions per pair for the reduction alone).
+// Here the two roles of a lane are separated:
+//   pass 1  lanes = PIXELS.  For one hit instance the per-pixel recurrences of the reference (T rebuilt by
+//           division, the accumulated colour behind the instance; backward.cu:842-1013) collapse, for a colour
+//           cotangent, into two scalars per pixel — the blend weight aT = alpha*T and q = G * dL/dopacity_term —
+//           because every one of the ten per-Gaussian derivatives is LINEAR in (aT, q) with coefficients that depend
+//           only on the pixel position and the instance.  The two scalars are staged in a per-warp [16 hits][32 px]
+//           shared-memory tile (one conflict-free 8-byte store per pair).
+//   pass 2  lanes = INSTANCES.  After 16 hits, lane (j, h) walks the 16 pixels of half h of the block for hit j and
+//           accumulates the ten sums in registers (no cross-lane reduction at all; the two halves are combined
+//           with one shuffle per value), then writes them to the warp's private accumulator row of the instance's
+//           batch slot — once, with plain stores.
+// Shared-memory wavefronts per pair drop from 27 to ~11 and instructions from 113 to ~80.
+// Same traversal order, same culling, same records as the kernel above; per-pixel activity tests use the same
+// bit-pinned power / expf / alpha chain as the forward pass, so exactly the forward's contributors are visited.
+// ---------------------------------------------------------------------------------------------
+#define BWD2_GROUP 16
+#define BWD2_STRIDE 33  // staged float2 per hit: 32 pixels + 1 pad (conflict-free for both access patterns)
+
+__device__ __forceinline__ float2 lds64_at(uint32_t addr) {
+  float2 v;
+  asm volatile("ld.shared.v2.f32 {%0,%1}, [%2];" : "=f"(v.x), "=f"(v.y) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float4 lds128_at(uint32_t addr) {
+  float4 v;
+  asm volatile("ld.shared.v4.f32 {%0,%1,%2,%3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ void sts64_at(uint32_t addr, float a, float b) {
+  asm volatile("st.shared.v2.f32 [%0], {%1,%2};" ::"r"(addr), "f"(a), "f"(b) : "memory");
+}
+__device__ __forceinline__ void sts128_at(uint32_t addr, float a, float b, float c, float d) {
+  asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
+}
+
+template <int BATCH, int MINB>
+__global__ void __launch_bounds__(256, MINB)
+blend_bwd2_kernel(BlendBwdParams p) {
+  constexpr int NS = 16;  // floats per gradient record in global memory
+  constexpr int AS = 12;  // accumulator stride per batch slot (10 values + 2 pad words: 16-byte rows)
+  constexpr int G = BWD2_GROUP;
+  static_assert(BATCH <= 255, "hit queue entries are bytes");
+  __shared__ float4 s_rec[BATCH * 3];     // survivors: {x, y, conic.x, conic.y} {conic.z, opacity, r, g} {blue, tau, position, slot}
+  __shared__ float4 s_rawh[BATCH * 2];    // cp.async landing zone of the NEXT batch: heads as fetched (entry t: thread t's)
+  __shared__ float s_rawb[BATCH];         //   blue
+  __shared__ uint32_t s_rawe[BATCH];      //   emission slot
+  __shared__ uint32_t s_e[BATCH];
+  __shared__ uint8_t s_queue[8 * BATCH];  // per warp: shared-memory indices of the survivors that hit the warp's block
+  __shared__ uint32_t s_wcount[8];
+  __shared__ uint32_t s_red[8];
+  extern __shared__ __align__(16) float s_dyn[];
+  float* s_acc = s_dyn;                                             // [8 warps][BATCH][AS]
+  float* s_stage = s_dyn + 8 * BATCH * AS;                          // [8 warps][G][33] float2 (aT, q)
+  float4* s_pix = reinterpret_cast<float4*>(s_stage + 8 * G * BWD2_STRIDE * 2);  // [8 warps][34] {dLp r, g, b, -}
+
+  const int tiles = p.tiles_x * p.tiles_y;
+  const int gt = blockIdx.x;
+  const int v = gt / tiles;
+  const int t = gt - v * tiles;
+  const int tyi = t / p.tiles_x, txi = t - tyi * p.tiles_x;
+  const int w = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int wx0 = txi * IGS_TILE_X + (w & 1) * 8;
+  const int wy0 = tyi * IGS_TILE_Y + (w >> 1) * 4;
+  const int pxi = wx0 + (lane & 7), pyi = wy0 + (lane >> 3);
+  const bool inside = pxi < p.W && pyi < p.H;
+  const size_t N = (size_t)p.W * p.H;
+  const size_t pix_id = (size_t)p.W * pyi + pxi;
+  const float pixfx = (float)pxi, pixfy = (float)pyi;
+  const float tx0 = (float)(txi * IGS_TILE_X), ty0 = (float)(tyi * IGS_TILE_Y);
+  const float tx1 = (float)(min(txi * IGS_TILE_X + IGS_TILE_X, p.W) - 1);
+  const float ty1 = (float)(min(tyi * IGS_TILE_Y + IGS_TILE_Y, p.H) - 1);
+  const float bx0 = (float)wx0, by0 = (float)wy0;
+  const float bx1 = (float)min(wx0 + 7, p.W - 1), by1 = (float)min(wy0 + 3, p.H - 1);
+  const uint32_t rec_base = smem_addr(s_rec);
+  const uint32_t acc_base = smem_addr(s_acc) + (uint32_t)w * (BATCH * AS * 4);
+  const uint32_t stage_base = smem_addr(s_stage) + (uint32_t)w * (G * BWD2_STRIDE * 8);
+  const uint32_t stage_wr = stage_base + (uint32_t)lane * 8;  // + i * 33 * 8 for hit i of the group
+  // pass-2 role of this lane: hit j of the group, pixel rows {2h, 2h+1} of the block
+  const uint32_t j = (uint32_t)lane & 15u, h = (uint32_t)lane >> 4;
+  const uint32_t stage_rd = stage_base + (j * BWD2_STRIDE + 16u * h) * 8;  // + s * 8 for pixel 16h + s
+  // pixel records are stored at index p + (p >> 4): the pad keeps the two halves' 16-byte reads in different banks
+  const uint32_t pix_base = smem_addr(s_pix) + (uint32_t)w * (34 * 16);
+  const uint32_t pix_rd = pix_base + (16u * h + h) * 16;  // + s * 16
+  uint8_t* const queue = s_queue + w * BATCH;
+  const uint32_t rawh_addr = smem_addr(s_rawh) + threadIdx.x * 32;
+  const uint32_t rawb_addr = smem_addr(s_rawb) + threadIdx.x * 4;
+  const uint32_t rawe_addr = smem_addr(s_rawe) + threadIdx.x * 4;
+  for (uint32_t f = threadIdx.x; f < 8 * BATCH * AS; f += 256) s_acc[f] = 0.0f;
+
+  const uint2 range = p.ranges[gt];
+  const uint32_t last_contributor = inside ? p.n_contrib[(size_t)v * 2 * N + pix_id] : 0u;
+
+  uint32_t wlast = last_contributor;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) wlast = max(wlast, __shfl_xor_sync(0xffffffffu, wlast, o));
+  if (lane == 0) s_red[w] = wlast;
+
+  const float w_final = inside ? p.alphas[(size_t)v * N + pix_id] : 0.0f;
+  const float T_final = inside ? (1.0f - w_final) : 0.0f;
+  float dLp0 = 0, dLp1 = 0, dLp2 = 0, dL_dalpha = 0;
+  if (inside) {
+    const float* g = p.dL_color + (size_t)v * 3 * N;
+    dLp0 = g[pix_id]; dLp1 = g[N + pix_id]; dLp2 = g[2 * N + pix_id];
+    if (p.dL_alpha) dL_dalpha = p.dL_alpha[(size_t)v * N + pix_id];
+  }
+  sts128_at(pix_base + ((uint32_t)lane + ((uint32_t)lane >> 4)) * 16, dLp0, dLp1, dLp2, 0.0f);
+  // The alpha cotangent and the background enter dL/dopacity of instance i only as
+  //   T_final / (1 - alpha_i) * (dL/dalpha - bg . dL/dpixel):
+  // the reference's accumulated-alpha recurrence (backward.cu:972-975) telescopes, 1 - accum_alpha_rec = T_final / T_behind.
+  const float Kpix = T_final * (dL_dalpha - (p.bg[0] * dLp0 + p.bg[1] * dLp1 + p.bg[2] * dLp2));
+  const f32x2 pix2 = pack2(pixfx, pixfy);
+  __syncthreads();
+  uint32_t tile_last = 0;
+#pragma unroll
+  for (int ww = 0; ww < 8; ww++) tile_last = max(tile_last, s_red[ww]);
+  const uint32_t end = range.x + tile_last;  // instances [end, range.y) were never blended
+
+  // ---- software pipeline of the batch fetch (north_star (3): asynchronous shared-memory staging) ----
+  // The list entry -> head gather is two dependent global loads.  They are taken off the critical path:
+  //   * the Gaussian id of a batch is loaded into a register TWO batches ahead,
+  //   * its head / blue / emission slot are copied global -> shared with cp.async ONE batch ahead,
+  // both while the warps traverse the current batch; a batch therefore starts from data already in shared memory.
+  // Every thread copies, waits for and reads only ITS OWN landing-zone entry, so no barrier is needed for it.
+  auto issue_copies = [&](uint32_t hi_b, uint32_t gid_b) {
+    const uint32_t lo_b = (hi_b - range.x > BATCH) ? hi_b - BATCH : range.x;
+    if (threadIdx.x < hi_b - lo_b) {
+      const float4* hp = reinterpret_cast<const float4*>(p.head + gid_b);
+      cp_async16(rawh_addr, hp);
+      cp_async16(rawh_addr + 16, hp + 1);
+      cp_async4(rawb_addr, &p.tail[gid_b].a.x);
+      cp_async4(rawe_addr, p.point_e + (hi_b - 1 - threadIdx.x));
+    }
+    cp_async_commit();
+  };
+  auto load_gid = [&](uint32_t hi_b) -> uint32_t {  // list entry of this thread in the batch that ends at hi_b
+    if (hi_b <= range.x) return 0u;
+    const uint32_t lo_b = (hi_b - range.x > BATCH) ? hi_b - BATCH : range.x;
+    return (threadIdx.x < hi_b - lo_b) ? p.point_list[hi_b - 1 - threadIdx.x] : 0u;
+  };
+  uint32_t gid_next = 0;
+  if (end > range.x) {
+    issue_copies(end, load_gid(end));
+    gid_next = load_gid((end - range.x > BATCH) ? end - BATCH : range.x);
+  }
+
+  // zero records of never-visited instances
+  for (uint32_t f = (end - range.x) * (NS / 4) + threadIdx.x; f < (range.y - range.x) * (NS / 4); f += 256) {
+    uint32_t jj = range.x + f / (NS / 4);
+    reinterpret_cast<float4*>(p.grec + (size_t)p.point_e[jj] * NS)[f % (NS / 4)] = make_float4(0, 0, 0, 0);
+  }
+
+  // per-pixel state of the back-to-front traversal: T (transmittance in front of the last visited contributor) and
+  // A = sum_c accum_rec_c * dL/dpixel_c, the accumulated colour BEHIND the next instance dotted with the cotangent
+  float T = T_final, A = 0.0f;
+
+  for (uint32_t hi = end; hi > range.x;) {
+    const uint32_t lo = (hi - range.x > BATCH) ? hi - BATCH : range.x;
+    const uint32_t nb = hi - lo;
+    // ---- 1. this batch's entries (already in shared memory), tile cull, ordered compaction ----
+    cp_async_wait_all();
+    bool keep = false;
+    float4 ha, hb;
+    float ex = 0, ey = 0, tau = 0, blue = 0;
+    uint32_t e_mine = 0;
+    if (threadIdx.x < nb) {
+      ha = lds128_at(rawh_addr);
+      hb = lds128_at(rawh_addr + 16);
+      blue = s_rawb[threadIdx.x];
+      e_mine = s_rawe[threadIdx.x];
+      keep = alpha_extent(ha.z, ha.w, hb.x, hb.y, ex, ey, tau);
+      keep = keep && (ha.x + ex >= tx0) && (ha.x - ex <= tx1) && (ha.y + ey >= ty0) && (ha.y - ey <= ty1);
+    }
+    uint32_t bal = __ballot_sync(0xffffffffu, keep);
+    if (lane == 0) s_wcount[w] = __popc(bal);
+    __syncthreads();  // (also: every thread has finished the record write-out of the previous batch)
+    uint32_t woff = 0, count = 0;
+#pragma unroll
+    for (int ww = 0; ww < 8; ww++) {
+      uint32_t c = s_wcount[ww];
+      if (ww < w) woff += c;
+      count += c;
+    }
+    if (threadIdx.x < nb) s_e[threadIdx.x] = e_mine;
+    if (keep) {
+      uint32_t k = woff + __popc(bal & ((1u << lane) - 1u));
+      s_rec[k] = ha;
+      s_rec[BATCH + k] = hb;
+      s_rec[2 * BATCH + k] = make_float4(blue, tau, __uint_as_float(hi - threadIdx.x - range.x), __uint_as_float(threadIdx.x));
+    }
+    // next batch: global -> shared copies now, its successor's list entries into a register
+    if (lo > range.x) {
+      issue_copies(lo, gid_next);
+      gid_next = load_gid((lo - range.x > BATCH) ? lo - BATCH : range.x);
+    }
+    __syncthreads();
+    // ---- 2. per-warp traversal ----
+    // 2a. survivors against this warp's 8x4 block -> queue of hits (in list order)
+    uint32_t qn = 0;
+    for (uint32_t base = 0; base < count; base += 32) {
+      const uint32_t k = base + lane;
+      bool hit = false;
+      if (k < count) {
+        const uint32_t ak = rec_base + k * 16;
+        const float4 a = lds128<0>(ak);
+        const float4 b = lds128<BATCH * 16>(ak);
+        const float4 c = lds128<BATCH * 32>(ak);
+        hit = (__float_as_uint(c.z) <= wlast) && block_can_contribute(a.x, a.y, a.z, a.w, b.x, c.y, bx0, by0, bx1, by1);
+      }
+      const uint32_t m = __ballot_sync(0xffffffffu, hit);
+      if (hit) queue[qn + __popc(m & ((1u << lane) - 1u))] = (uint8_t)k;
+      qn += __popc(m);
+    }
+    __syncwarp();
+    for (uint32_t g0 = 0; g0 < qn; g0 += G) {
+      const uint32_t ng = min((uint32_t)G, qn - g0);
+      // ---- pass 1: lanes = pixels, one hit per iteration ----
+#pragma unroll 2
+      for (uint32_t i = 0; i < ng; i++) {
+        const uint32_t kk = queue[g0 + i];
+        const uint32_t ak = rec_base + kk * 16;
+        const float4 a = lds128<0>(ak);
+        const float4 bq = lds128<BATCH * 16>(ak);
+        const float2 cq = lds64<BATCH * 32>(ak);             // {blue, -}
+        const uint32_t pos = __float_as_uint(lds32<BATCH * 32 + 8>(ak));
+        float dx, dy;
+        unpack2(sub2(pack2(a.x, a.y), pix2), dx, dy);  // each rounded like fsub()
+        const float power = splat_power(dx, dy, a.z, a.w, bq.x);
+        const float Gv = expf(power);
+        const float alpha = fminf(0.99f, fmul(bq.y, Gv));
+        const bool active = (pos <= last_contributor) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
+        // reference: T = T / (1 - alpha) and (-T_final / (1 - alpha)); one reciprocal serves both.  Evaluated on every
+        // lane and selected (1 - alpha is in [0.01, 1] wherever the result is kept).
+        float rcp;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(rcp) : "f"(1.0f - alpha));
+        const float Tn = T * rcp;
+        const float cd = fmaf(cq.x, dLp2, fmaf(bq.w, dLp1, bq.z * dLp0));  // colour . dL/dpixel
+        const float diff = cd - A;
+        const float qv = Gv * fmaf(diff, Tn, Kpix * rcp);  // G * ("dL_dopa" of the reference)
+        sts64_at(stage_wr + i * (BWD2_STRIDE * 8), active ? alpha * Tn : 0.0f, active ? qv : 0.0f);
+        T = active ? Tn : T;
+        A = active ? fmaf(alpha, diff, A) : A;  // accumulated colour behind the NEXT instance
+      }
+      // ---- pass 2: lanes = (hit j of the group, half h of the block) ----
+      __syncwarp();
+      const uint32_t kj = queue[g0 + (j < ng ? j : 0u)];
+      const uint32_t ak = rec_base + kj * 16;
+      const float4 a = lds128<0>(ak);
+      const float4 bq = lds128<BATCH * 16>(ak);
+      const float slot_bits = lds32<BATCH * 32 + 12>(ak);
+      const float gx = a.x - bx0;
+      const float gy = (a.y - by0) - (float)(2u * h);
+      float v0 = 0, v1 = 0, v2 = 0, v9 = 0, s6 = 0, s7 = 0, s8 = 0, a3 = 0, a4 = 0, b3 = 0, b4 = 0;
+#pragma unroll
+      for (int r = 0; r < 2; r++) {
+        const float ddy = gy - (float)r;
+        const float cydy = a.w * ddy, czdy = bq.x * ddy;
+#pragma unroll
+        for (int c = 0; c < 8; c++) {
+          const int s = r * 8 + c;
+          const float2 st = lds64_at(stage_rd + s * 8);
+          const float4 dl = lds128_at(pix_rd + s * 16);
+          const float ddx = gx - (float)c;
+          v0 = fmaf(st.x, dl.x, v0);
+          v1 = fmaf(st.x, dl.y, v1);
+          v2 = fmaf(st.x, dl.z, v2);
+          v9 += st.y;
+          const float qdx = st.y * ddx, qdy = st.y * ddy;
+          s6 = fmaf(qdx, ddx, s6);
+          s7 = fmaf(qdx, ddy, s7);
+          s8 = fmaf(qdy, ddy, s8);
+          a3 += qdx;
+          a4 += qdy;
+          b3 += fabsf(st.y * fmaf(a.z, ddx, cydy));
+          b4 += fabsf(st.y * fmaf(a.w, ddx, czdy));
+        }
+      }
+      v0 += __shfl_xor_sync(0xffffffffu, v0, 16); v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
+      v2 += __shfl_xor_sync(0xffffffffu, v2, 16); v9 += __shfl_xor_sync(0xffffffffu, v9, 16);
+      s6 += __shfl_xor_sync(0xffffffffu, s6, 16); s7 += __shfl_xor_sync(0xffffffffu, s7, 16);
+      s8 += __shfl_xor_sync(0xffffffffu, s8, 16); a3 += __shfl_xor_sync(0xffffffffu, a3, 16);
+      a4 += __shfl_xor_sync(0xffffffffu, a4, 16); b3 += __shfl_xor_sync(0xffffffffu, b3, 16);
+      b4 += __shfl_xor_sync(0xffffffffu, b4, 16);
+      if (h == 0 && j < ng) {
+        // dL/dG = opacity * dL_dopa;  dG/ddelx = -G (cx dx + cy dy), dG/ddely = -G (cy dx + cz dy);
+        // dL/dconic = -0.5 G d d^T dL/dG;  |grad| accumulates the per-pixel absolute values
+        const float o = bq.y;
+        const float mo = -o, ho = -0.5f * o;
+        const uint32_t aa = acc_base + __float_as_uint(slot_bits) * (uint32_t)(AS * 4);
+        sts128_at(aa, v0, v1, v2, mo * fmaf(a.z, a3, a.w * a4) * p.half_w);
+        sts128_at(aa + 16, mo * fmaf(a.w, a3, bq.x * a4) * p.half_h, o * fmaf(p.half_w, b3, p.half_h * b4), ho * s6, ho * s7);
+        sts64_at(aa + 32, ho * s8, v9);
+      }
+      __syncwarp();
+    }
+    __syncthreads();
+    // ---- 3. one dense record per instance of this batch: sum (and clear) the 8 warps' accumulators ----
+    // 16 bytes of a record per thread: three quarters come from the accumulators (values 0-9; words 10, 11 are pad
+    // and stay zero), the fourth is zero so that every 32-byte sector is written whole
+    for (uint32_t f = threadIdx.x; f < nb * 4; f += 256) {
+      const uint32_t sl = f >> 2, q4 = f & 3;
+      float4 sum = make_float4(0, 0, 0, 0);
+      if (q4 < 3) {
+#pragma unroll
+        for (int ww = 0; ww < 8; ww++) {
+          float4* pa = reinterpret_cast<float4*>(s_acc + ((size_t)ww * BATCH + sl) * AS) + q4;
+          const float4 x = *pa;
+          sum.x += x.x; sum.y += x.y; sum.z += x.z; sum.w += x.w;
+          *pa = make_float4(0, 0, 0, 0);
+        }
+      }
+      reinterpret_cast<float4*>(p.grec + (size_t)s_e[sl] * NS)[q4] = sum;
+    }
+    // no barrier here: the next batch touches s_e / s_rec / s_acc only after its first barrier
+    hi = lo;
+  }
+}
+
 int blend_bwd_record_floats(bool geograd) { return geograd ? 32 : 16; }
 
 template <bool C, bool D, bool N, bool G, int MINB>
@@ -434,6 +759,15 @@ static void launch_one(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
   blend_bwd_kernel<C, D, N, G, MINB><<<nblocks, 256, bytes, s>>>(p);
 }
 
+template <int BATCH, int MINB>
+static void launch_two_pass(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
+  // dynamic shared memory: per-warp accumulators + per-warp (aT, q) staging tiles + per-warp pixel records
+  constexpr int bytes = 8 * BATCH * 12 * 4 + 8 * BWD2_GROUP * BWD2_STRIDE * 8 + 8 * 34 * 16;
+  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  blend_bwd2_kernel<BATCH, MINB><<<nblocks, 256, bytes, s>>>(p);
+}
+
 void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s) {
   int nblocks = V * p.tiles_x * p.tiles_y;
   if (nblocks <= 0) return;
@@ -441,7 +775,14 @@ void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bo
   // IGS_BWD_OCC=4 selects the 64-register / 96-instance-batch build of the colour-only kernel (4 CTAs/SM)
   static const int occ = [] { const char* e = getenv("IGS_BWD_OCC"); return e ? atoi(e) : 4; }();
   if (!geograd || (!coord && !depth)) {
-    if (occ >= 4) launch_one<false, false, false, false, 4>(p, nblocks, s);
+    // IGS_BWD_IMPL=1 selects the first-generation colour-only kernel (reduction per pair); default: two-pass kernel
+    static const int impl = [] { const char* e = getenv("IGS_BWD_IMPL"); return e ? atoi(e) : 2; }();
+    static const int cfg = [] { const char* e = getenv("IGS_BWD2_CFG"); return e ? atoi(e) : 0; }();
+    if (impl >= 2) {
+      if (cfg == 1) launch_two_pass<128, 2>(p, nblocks, s);
+      else if (cfg == 2) launch_two_pass<160, 2>(p, nblocks, s);
+      else launch_two_pass<72, 3>(p, nblocks, s);
+    } else if (occ >= 4) launch_one<false, false, false, false, 4>(p, nblocks, s);
     else launch_one<false, false, false, false, 3>(p, nblocks, s);
   } else if (coord && depth) launch_one<true, true, true, true, 2>(p, nblocks, s);
   else if (coord) launch_one<true, false, true, true, 2>(p, nblocks, s);
