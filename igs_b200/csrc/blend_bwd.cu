@@ -472,12 +472,12 @@ blend_bwd2_kernel(BlendBwdParams p) {
   constexpr int NS = 16;  // floats per gradient record in global memory
   constexpr int AS = 12;  // accumulator stride per batch slot (10 values + 2 pad words: 16-byte rows)
   constexpr int G = BWD2_GROUP;
-  static_assert(BATCH <= 255, "hit queue entries are bytes");
+  static_assert(BATCH <= 255 && BATCH % 32 == 0, "hit queue entries are bytes; whole 32-entry segments");
   __shared__ float4 s_rec[BATCH * 3];     // survivors: {x, y, conic.x, conic.y} {conic.z, opacity, r, g} {blue, tau, position, slot}
   __shared__ float4 s_rawh[BATCH * 2];    // cp.async landing zone of the NEXT batch: heads as fetched (entry t: thread t's)
   __shared__ float s_rawb[BATCH];         //   blue
   __shared__ uint32_t s_rawe[BATCH];      //   emission slot
-  __shared__ uint32_t s_e[BATCH];
+  __shared__ uint32_t s_e[2 * BATCH];     // emission slots of the batch, double-buffered (read by the previous batch's write-out)
   __shared__ uint8_t s_queue[8 * BATCH];  // per warp: shared-memory indices of the survivors that hit the warp's block
   __shared__ uint32_t s_wcount[8];
   __shared__ uint32_t s_red[8];
@@ -586,37 +586,31 @@ blend_bwd2_kernel(BlendBwdParams p) {
   // per-pixel state of the back-to-front traversal: T (transmittance in front of the last visited contributor) and
   // A = sum_c accum_rec_c * dL/dpixel_c, the accumulated colour BEHIND the next instance dotted with the cotangent
   float T = T_final, A = 0.0f;
+  uint32_t parity = 0;
 
   for (uint32_t hi = end; hi > range.x;) {
     const uint32_t lo = (hi - range.x > BATCH) ? hi - BATCH : range.x;
     const uint32_t nb = hi - lo;
-    // ---- 1. this batch's entries (already in shared memory), tile cull, ordered compaction ----
+    // ---- 1. this batch's entries (already in shared memory), tile cull, compaction ----
+    // Survivors are compacted INSIDE each 32-entry segment (warp w's entries go to s_rec[32 w ...]), so no cross-warp
+    // prefix and no barrier is needed before the writes; list order is segment order, then order inside the segment.
     cp_async_wait_all();
     bool keep = false;
     float4 ha, hb;
     float ex = 0, ey = 0, tau = 0, blue = 0;
-    uint32_t e_mine = 0;
+    uint32_t* const e_cur = s_e + (parity ? BATCH : 0);
     if (threadIdx.x < nb) {
       ha = lds128_at(rawh_addr);
       hb = lds128_at(rawh_addr + 16);
       blue = s_rawb[threadIdx.x];
-      e_mine = s_rawe[threadIdx.x];
+      e_cur[threadIdx.x] = s_rawe[threadIdx.x];
       keep = alpha_extent(ha.z, ha.w, hb.x, hb.y, ex, ey, tau);
       keep = keep && (ha.x + ex >= tx0) && (ha.x - ex <= tx1) && (ha.y + ey >= ty0) && (ha.y - ey <= ty1);
     }
-    uint32_t bal = __ballot_sync(0xffffffffu, keep);
+    const uint32_t bal = __ballot_sync(0xffffffffu, keep);
     if (lane == 0) s_wcount[w] = __popc(bal);
-    __syncthreads();  // (also: every thread has finished the record write-out of the previous batch)
-    uint32_t woff = 0, count = 0;
-#pragma unroll
-    for (int ww = 0; ww < 8; ww++) {
-      uint32_t c = s_wcount[ww];
-      if (ww < w) woff += c;
-      count += c;
-    }
-    if (threadIdx.x < nb) s_e[threadIdx.x] = e_mine;
     if (keep) {
-      uint32_t k = woff + __popc(bal & ((1u << lane) - 1u));
+      const uint32_t k = (uint32_t)w * 32u + __popc(bal & ((1u << lane) - 1u));
       s_rec[k] = ha;
       s_rec[BATCH + k] = hb;
       s_rec[2 * BATCH + k] = make_float4(blue, tau, __uint_as_float(hi - threadIdx.x - range.x), __uint_as_float(threadIdx.x));
@@ -630,10 +624,10 @@ blend_bwd2_kernel(BlendBwdParams p) {
     // ---- 2. per-warp traversal ----
     // 2a. survivors against this warp's 8x4 block -> queue of hits (in list order)
     uint32_t qn = 0;
-    for (uint32_t base = 0; base < count; base += 32) {
-      const uint32_t k = base + lane;
+    for (uint32_t seg = 0; seg * 32 < nb; seg++) {
+      const uint32_t k = seg * 32 + lane;
       bool hit = false;
-      if (k < count) {
+      if ((uint32_t)lane < s_wcount[seg]) {
         const uint32_t ak = rec_base + k * 16;
         const float4 a = lds128<0>(ak);
         const float4 b = lds128<BATCH * 16>(ak);
@@ -654,8 +648,8 @@ blend_bwd2_kernel(BlendBwdParams p) {
         const uint32_t ak = rec_base + kk * 16;
         const float4 a = lds128<0>(ak);
         const float4 bq = lds128<BATCH * 16>(ak);
-        const float2 cq = lds64<BATCH * 32>(ak);             // {blue, -}
-        const uint32_t pos = __float_as_uint(lds32<BATCH * 32 + 8>(ak));
+        const float4 cq = lds128<BATCH * 32>(ak);  // {blue, tau, position, slot}
+        const uint32_t pos = __float_as_uint(cq.z);
         float dx, dy;
         unpack2(sub2(pack2(a.x, a.y), pix2), dx, dy);  // each rounded like fsub()
         const float power = splat_power(dx, dy, a.z, a.w, bq.x);
@@ -681,33 +675,46 @@ blend_bwd2_kernel(BlendBwdParams p) {
       const float4 a = lds128<0>(ak);
       const float4 bq = lds128<BATCH * 16>(ak);
       const float slot_bits = lds32<BATCH * 32 + 12>(ak);
+      // Every per-Gaussian sum is linear in (aT, q) with coefficients that are polynomials of the pixel offset
+      // d = centre - pixel.  With the pixel at column c, row r of this lane's half (d = (gx - c, gy - r)) the q-sums
+      // expand into MOMENTS of q over the half, which need no per-pixel geometry at all:
+      //   sum q dx   = gx S0 - Sx                  sum q dx^2  = gx^2 S0 - 2 gx Sx + Sxx
+      //   sum q dy   = gy S0 - Sy                  sum q dx dy = gx gy S0 - gx Sy - gy Sx + Sxy
+      //                                            sum q dy^2  = gy^2 S0 - 2 gy Sy + Syy
+      // (S0 = sum q, Sx = sum q c, Sxx = sum q c^2, ...; with two rows r in {0, 1}: Sy = Syy = row-1 sum, Sxy = row-1 Sx).
+      // Only the |.| sums of dL/dmean2D still need d per pixel.
       const float gx = a.x - bx0;
       const float gy = (a.y - by0) - (float)(2u * h);
-      float v0 = 0, v1 = 0, v2 = 0, v9 = 0, s6 = 0, s7 = 0, s8 = 0, a3 = 0, a4 = 0, b3 = 0, b4 = 0;
+      float v0 = 0, v1 = 0, v2 = 0, b3 = 0, b4 = 0;
+      float R0[2], R1[2], R2[2];
 #pragma unroll
       for (int r = 0; r < 2; r++) {
         const float ddy = gy - (float)r;
-        const float cydy = a.w * ddy, czdy = bq.x * ddy;
+        const float ub = fmaf(a.z, gx, a.w * ddy), wb = fmaf(a.w, gx, bq.x * ddy);  // cx dx + cy dy, cy dx + cz dy at c = 0
+        float r0 = 0, r1 = 0, r2 = 0;
 #pragma unroll
         for (int c = 0; c < 8; c++) {
           const int s = r * 8 + c;
           const float2 st = lds64_at(stage_rd + s * 8);
           const float4 dl = lds128_at(pix_rd + s * 16);
-          const float ddx = gx - (float)c;
           v0 = fmaf(st.x, dl.x, v0);
           v1 = fmaf(st.x, dl.y, v1);
           v2 = fmaf(st.x, dl.z, v2);
-          v9 += st.y;
-          const float qdx = st.y * ddx, qdy = st.y * ddy;
-          s6 = fmaf(qdx, ddx, s6);
-          s7 = fmaf(qdx, ddy, s7);
-          s8 = fmaf(qdy, ddy, s8);
-          a3 += qdx;
-          a4 += qdy;
-          b3 += fabsf(st.y * fmaf(a.z, ddx, cydy));
-          b4 += fabsf(st.y * fmaf(a.w, ddx, czdy));
+          r0 += st.y;
+          if (c > 0) r1 = fmaf(st.y, (float)c, r1);
+          if (c > 0) r2 = fmaf(st.y, (float)(c * c), r2);
+          b3 += fabsf(st.y * fmaf(-a.z, (float)c, ub));
+          b4 += fabsf(st.y * fmaf(-a.w, (float)c, wb));
         }
+        R0[r] = r0; R1[r] = r1; R2[r] = r2;
       }
+      const float S0 = R0[0] + R0[1], Sx = R1[0] + R1[1], Sxx = R2[0] + R2[1], Sy = R0[1], Sxy = R1[1];
+      float v9 = S0;
+      float a3 = fmaf(gx, S0, -Sx);
+      float a4 = fmaf(gy, S0, -Sy);
+      float s6 = fmaf(gx, fmaf(gx, S0, -2.0f * Sx), Sxx);
+      float s7 = fmaf(gx, fmaf(gy, S0, -Sy), fmaf(-gy, Sx, Sxy));
+      float s8 = fmaf(gy, fmaf(gy, S0, -2.0f * Sy), Sy);
       v0 += __shfl_xor_sync(0xffffffffu, v0, 16); v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
       v2 += __shfl_xor_sync(0xffffffffu, v2, 16); v9 += __shfl_xor_sync(0xffffffffu, v9, 16);
       s6 += __shfl_xor_sync(0xffffffffu, s6, 16); s7 += __shfl_xor_sync(0xffffffffu, s7, 16);
@@ -742,10 +749,11 @@ blend_bwd2_kernel(BlendBwdParams p) {
           *pa = make_float4(0, 0, 0, 0);
         }
       }
-      reinterpret_cast<float4*>(p.grec + (size_t)s_e[sl] * NS)[q4] = sum;
+      reinterpret_cast<float4*>(p.grec + (size_t)e_cur[sl] * NS)[q4] = sum;
     }
-    // no barrier here: the next batch touches s_e / s_rec / s_acc only after its first barrier
+    // no barrier here: the next batch writes the OTHER half of s_e, and s_rec / s_acc only change hands at its barrier
     hi = lo;
+    parity ^= 1u;
   }
 }
 
@@ -780,8 +788,8 @@ void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bo
     static const int cfg = [] { const char* e = getenv("IGS_BWD2_CFG"); return e ? atoi(e) : 0; }();
     if (impl >= 2) {
       if (cfg == 1) launch_two_pass<128, 2>(p, nblocks, s);
-      else if (cfg == 2) launch_two_pass<160, 2>(p, nblocks, s);
-      else launch_two_pass<72, 3>(p, nblocks, s);
+      else if (cfg == 2) launch_two_pass<96, 2>(p, nblocks, s);
+      else launch_two_pass<64, 3>(p, nblocks, s);
     } else if (occ >= 4) launch_one<false, false, false, false, 4>(p, nblocks, s);
     else launch_one<false, false, false, false, 3>(p, nblocks, s);
   } else if (coord && depth) launch_one<true, true, true, true, 2>(p, nblocks, s);
