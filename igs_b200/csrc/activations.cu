@@ -8,6 +8,7 @@
 // forward is one launch over P Gaussians and the backward one launch that writes straight into the packed
 // [P*59] gradient record, so the refine step needs no autograd graph at all.
 #include "common.cuh"
+#include <cmath>
 #include "kernels.cuh"
 
 namespace igs {
@@ -117,6 +118,80 @@ void launch_adam_groups(float* p, const float* g, float* m, float* v, int ngroup
   if (nb > 148 * 16) nb = 148 * 16;
   count_launch();
   adam_groups_kernel<<<(unsigned)nb, 256, 0, s>>>(p, g, m, v, off, gr, b1, b2, eps, inv_sqrt_bc2);
+}
+
+// Guarded Adam: the same update, but (a) a no-op when *skip != 0 (a capacity-mode forward that overflowed) and (b) with the
+// step count optionally read from device memory, so that a CUDA-graph replay advances it (bias corrections in double
+// like torch's Python-side `1 - beta ** step`).
+__global__ void __launch_bounds__(256)
+adam_groups_guarded_kernel(float* __restrict__ p, const float* __restrict__ g, float* __restrict__ m, float* __restrict__ v,
+                           size_t n, AdamGroups gr, float b1, float b2, float eps, float inv_sqrt_bc2_host,
+                           const unsigned int* __restrict__ skip, const int* __restrict__ step_dev) {
+  // step_dev == nullptr: gr.step_size[] / inv_sqrt_bc2_host are the host-computed step sizes (exactly the unguarded
+  // kernel's arithmetic); otherwise gr.step_size[] holds the learning rates and the corrections are computed here.
+  if (skip != nullptr && *skip != 0u) return;
+  __shared__ float s_step[8];
+  __shared__ float s_inv_sqrt_bc2;
+  if (threadIdx.x == 0) {
+    if (step_dev != nullptr) {
+      const int t = *step_dev + 1;
+      const double bc1 = 1.0 - pow((double)b1, (double)t);
+      const double bc2 = 1.0 - pow((double)b2, (double)t);
+      for (int k = 0; k < 8; k++) s_step[k] = (float)((double)gr.step_size[k] / bc1);
+      s_inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+    } else {
+      for (int k = 0; k < 8; k++) s_step[k] = gr.step_size[k];
+      s_inv_sqrt_bc2 = inv_sqrt_bc2_host;
+    }
+  }
+  __syncthreads();
+  const float inv_sqrt_bc2 = s_inv_sqrt_bc2;
+  size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+  const size_t stride = (size_t)gridDim.x * blockDim.x;
+  for (; i < n; i += stride) {
+    float step_size = s_step[0];
+#pragma unroll
+    for (int k = 1; k < 8; k++)
+      if (k < gr.n && i >= gr.end[k - 1]) step_size = s_step[k];
+    const float gi = g[i];
+    const float mi = m[i] + (1.0f - b1) * (gi - m[i]);
+    const float vi = b2 * v[i] + (1.0f - b2) * gi * gi;
+    m[i] = mi;
+    v[i] = vi;
+    const float denom = sqrtf(vi) * inv_sqrt_bc2 + eps;
+    p[i] = p[i] - step_size * (mi / denom);
+  }
+}
+
+__global__ void adam_step_advance_kernel(int* step_dev, const unsigned int* skip) {
+  if (skip != nullptr && *skip != 0u) return;
+  *step_dev += 1;
+}
+
+void launch_adam_groups_guarded(float* p, const float* g, float* m, float* v, int ngroups, const size_t* sizes,
+                                const float* lrs, float b1, float b2, float eps, int step, const unsigned int* skip,
+                                int* step_dev, cudaStream_t s) {
+  AdamGroups gr;
+  gr.n = ngroups;
+  size_t off = 0;
+  const double bc1 = 1.0 - pow((double)b1, (double)step), bc2 = 1.0 - pow((double)b2, (double)step);
+  for (int k = 0; k < 8; k++) {
+    if (k < ngroups) {
+      off += sizes[k];
+      gr.step_size[k] = step_dev ? lrs[k] : (float)((double)lrs[k] / bc1);
+    } else gr.step_size[k] = 0.0f;
+    gr.end[k] = off;
+  }
+  if (off == 0) return;
+  size_t nb = (off + 255) / 256;
+  if (nb > 148 * 16) nb = 148 * 16;
+  count_launch();
+  adam_groups_guarded_kernel<<<(unsigned)nb, 256, 0, s>>>(p, g, m, v, off, gr, b1, b2, eps,
+                                                          step_dev ? 0.0f : (float)(1.0 / sqrt(bc2)), skip, step_dev);
+  if (step_dev != nullptr) {   // after every block has read the step (stream order)
+    count_launch();
+    adam_step_advance_kernel<<<1, 1, 0, s>>>(step_dev, skip);
+  }
 }
 
 }  // namespace igs

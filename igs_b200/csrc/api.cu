@@ -90,9 +90,15 @@ __global__ void pack_cameras_kernel(int V, const float* __restrict__ view, const
   }
 }
 
-__global__ void write_header_kernel(Header* h, Header v, const uint32_t* total) {
-  v.R = total ? *total : 0u;
+// capacity == 0: R = the instance total.  capacity != 0 (capacity mode): the buffers were carved for `capacity`
+// instances, R = capacity; the true total and the overflow flag go to pad[0] / pad[1] (and to `status`, if given).
+__global__ void write_header_kernel(Header* h, Header v, const uint32_t* total, uint32_t capacity, uint32_t* status) {
+  const uint32_t t = total ? *total : 0u;
+  v.R = capacity ? capacity : t;
+  v.pad[0] = t;
+  v.pad[1] = (capacity != 0u && t > capacity) ? 1u : 0u;
   *h = v;
+  if (status) { status[0] = t; status[1] = v.pad[1]; }
 }
 __global__ void write_tag_kernel(BufTag* t, BufTag v) { *t = v; }
 
@@ -264,22 +270,30 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   hv.magic = IGS_MAGIC; hv.P = P; hv.V = V; hv.N = (uint32_t)N; hv.tiles_x = tiles_x; hv.tiles_y = tiles_y;
   hv.flags = (a->require_coord ? 1u : 0u) | (a->require_depth ? 2u : 0u) | (a->scales ? 8u : 0u) | (a->shs ? 16u : 0u) |
              ((uint32_t)cur << 8);
-  count_launch();
-  write_header_kernel<<<1, 1, 0, s>>>(G.hdr, hv, d_total);
-
-  // ---- the one host sync: instance count (reference rasterizer_impl.cu:354) ----
-  // read through a pinned word (one per host thread): a copy into pageable memory is staged by the driver
-  static thread_local uint32_t* pinned_R = nullptr;
-  if (pinned_R == nullptr && cudaHostAlloc(reinterpret_cast<void**>(&pinned_R), 64, cudaHostAllocPortable) != cudaSuccess) {
-    pinned_R = nullptr;
-    (void)cudaGetLastError();
+  // ---- the instance count ----
+  // Exact mode (instance_capacity == 0, the reference's behaviour, rasterizer_impl.cu:354): one host read of R through a
+  // pinned word, the binning buffers are sized for exactly R.  Capacity mode (instance_capacity > 0): NO host round-trip —
+  // the buffers are sized for the caller's capacity, every downstream launch is sized for it and reads the true count
+  // on the device; instances past the capacity are dropped and flagged (header pad[1], args->status[1]).
+  const bool capmode = a->instance_capacity > 0;
+  const uint32_t* n_dev = nullptr;
+  uint32_t R = 0;
+  if (!capmode) {
+    static thread_local uint32_t* pinned_R = nullptr;
+    if (pinned_R == nullptr && cudaHostAlloc(reinterpret_cast<void**>(&pinned_R), 64, cudaHostAllocPortable) != cudaSuccess) {
+      pinned_R = nullptr;
+      (void)cudaGetLastError();
+    }
+    uint32_t R_pageable = 0;
+    uint32_t* R_dst = pinned_R ? pinned_R : &R_pageable;
+    IGS_CUDA_CHECK(cudaMemcpyAsync(R_dst, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
+    IGS_CUDA_CHECK(cudaStreamSynchronize(s));
+    R = *R_dst;
+    if (R > 0x7FFFFFFFu) { set_error("too many instances: %u", R); return IGS_ERR_UNSUPPORTED; }
+  } else {
+    R = (uint32_t)a->instance_capacity;
+    n_dev = d_total;
   }
-  uint32_t R_pageable = 0;
-  uint32_t* R_dst = pinned_R ? pinned_R : &R_pageable;
-  IGS_CUDA_CHECK(cudaMemcpyAsync(R_dst, d_total, sizeof(uint32_t), cudaMemcpyDeviceToHost, s));
-  IGS_CUDA_CHECK(cudaStreamSynchronize(s));
-  const uint32_t R = *R_dst;
-  if (R > 0x7FFFFFFFu) { set_error("too many instances: %u", R); return IGS_ERR_UNSUPPORTED; }
 
   BinBuf bsz = carve_bin(nullptr, R);
   char* bptr = bin_alloc(bin_user, bsz.bytes);
@@ -293,20 +307,20 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   if (R > 0) {
     { StageScope st(IGS_STAGE_EMIT, s);
       launch_emit_instances(VP, (uint32_t)P, tiles_x, tiles_y, G.cams, sorted_gid, G.inst_off, G.head, G.radii, B.tkey[0],
-                            B.tval[0], B.inst_gid, s); }
+                            B.tval[0], B.inst_gid, R, s); }
     if (int e = debug_sync(dbg, s, "emit")) return e;
     { StageScope st(IGS_STAGE_TILE_SORT, s);
-      bcur = radix_sort_pairs<uint32_t>(B.tkey, B.tval, R, bits_for((uint64_t)V * tiles), B.hist, nullptr, s); }
+      bcur = radix_sort_pairs<uint32_t>(B.tkey, B.tval, R, bits_for((uint64_t)V * tiles), B.hist, n_dev, s); }
     if (int e = debug_sync(dbg, s, "tile sort")) return e;
     { StageScope st(IGS_STAGE_FINALIZE, s);
-      launch_finalize_bins(R, B.tkey[bcur], B.tval[bcur], B.inst_gid, B.point_list, I.ranges, s); }
+      launch_finalize_bins(R, n_dev, B.tkey[bcur], B.tval[bcur], B.inst_gid, B.point_list, I.ranges, s); }
     if (int e = debug_sync(dbg, s, "finalize bins")) return e;
   }
   // remember which ping-pong buffer holds the sorted instances (bit 16 of flags)
   {
     hv.flags |= ((uint32_t)bcur << 16);
     count_launch();
-    write_header_kernel<<<1, 1, 0, s>>>(G.hdr, hv, d_total);
+    write_header_kernel<<<1, 1, 0, s>>>(G.hdr, hv, d_total, capmode ? R : 0u, a->status);
     hv.R = R;
     std::lock_guard<std::mutex> lk(g_shadow_mu);
     if (g_shadow.size() > 4096) g_shadow.clear();
@@ -314,6 +328,7 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   }
 
   BlendFwdParams bp;
+  bp.counters = nullptr;
   bp.W = W; bp.H = H; bp.tiles_x = tiles_x; bp.tiles_y = tiles_y; bp.focal_x = focal_x; bp.focal_y = focal_y;
   bp.ranges = I.ranges; bp.point_list = B.point_list; bp.head = G.head; bp.tail = G.tail; bp.bg = a->background;
   bp.out_color = a->out_color; bp.out_coord = a->out_coord; bp.out_mcoord = a->out_mcoord; bp.out_depth = a->out_depth;
@@ -405,7 +420,7 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   }
 
   GatherBwdParams gp;
-  gp.P = P; gp.V = V; gp.W = W; gp.H = H; gp.ns = ns; gp.focal_x = focal_x; gp.focal_y = focal_y;
+  gp.P = P; gp.V = V; gp.W = W; gp.H = H; gp.ns = ns; gp.capacity = R; gp.focal_x = focal_x; gp.focal_y = focal_y;
   gp.tan_fovx = a->tan_fovx; gp.tan_fovy = a->tan_fovy; gp.kernel_size = a->kernel_size;
   gp.means3D = a->means3D; gp.cams = G.cams; gp.cov3D = G.cov3D; gp.eig = G.eig; gp.head = G.head; gp.radii = G.radii;
   gp.tiles = G.tiles; gp.rank = G.rank; gp.sorted_gid = G.sval[(hv.flags >> 8) & 1]; gp.inst_off = G.inst_off; gp.clamped = G.clamped; gp.grec = grec; gp.sums = sums;
@@ -449,7 +464,8 @@ int igs_decode_binning(int P, int V, int R, int width, int height, const char* g
   const int bcur = (hv.flags >> 16) & 1;
   if (R > 0 && binning_buffer) {
     BinBuf B = carve_bin(const_cast<char*>(binning_buffer), R);
-    launch_decode_keys((uint32_t)R, (uint32_t)tiles, (uint32_t)P, B.tkey[bcur], B.point_list, G.depth, out->keys,
+    const uint32_t n_true = hv.pad[0] < (uint32_t)R ? hv.pad[0] : (uint32_t)R;   // capacity mode: R is the capacity
+    launch_decode_keys(n_true, (uint32_t)tiles, (uint32_t)P, B.tkey[bcur], B.point_list, G.depth, out->keys,
                        out->point_list, s);
   }
   if (out->ranges) IGS_CUDA_CHECK(cudaMemcpyAsync(out->ranges, I.ranges, sizeof(uint2) * V * tiles, cudaMemcpyDeviceToDevice, s));
@@ -514,6 +530,48 @@ int igs_adam_step_groups(float* param, const float* grad, float* exp_avg, float*
   return IGS_OK;
 }
 
+int igs_adam_step_groups_guarded(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int ngroups,
+                                 const size_t* sizes, const float* lrs, float beta1, float beta2, float eps, int step,
+                                 const unsigned int* skip_if_nonzero, int* step_dev, void* stream) {
+  if (ngroups == 0) return IGS_OK;
+  if (ngroups < 0 || ngroups > 8 || !sizes || !lrs || !param || !grad || !exp_avg || !exp_avg_sq ||
+      (step_dev == nullptr && step < 1)) {
+    set_error("bad argument");
+    return IGS_ERR_INVALID;
+  }
+  {
+    StageScope st(IGS_STAGE_ADAM, (cudaStream_t)stream);
+    launch_adam_groups_guarded(param, grad, exp_avg, exp_avg_sq, ngroups, sizes, lrs, beta1, beta2, eps, step,
+                               skip_if_nonzero, step_dev, (cudaStream_t)stream);
+  }
+  IGS_CUDA_CHECK(cudaGetLastError());
+  return IGS_OK;
+}
+
+int igs_count_blend_pairs(int P, int V, int R, int width, int height, const char* geom_buffer, const char* binning_buffer,
+                          const char* image_buffer, unsigned long long* counts, void* stream) {
+  cudaStream_t s = (cudaStream_t)stream;
+  if (!geom_buffer || !image_buffer || !counts || P <= 0 || V < 1 || R < 0) { set_error("bad argument"); return IGS_ERR_INVALID; }
+  if (R == 0) return IGS_OK;
+  if (!binning_buffer) { set_error("bad argument"); return IGS_ERR_INVALID; }
+  const int tiles_x = (width + IGS_TILE_X - 1) / IGS_TILE_X, tiles_y = (height + IGS_TILE_Y - 1) / IGS_TILE_Y;
+  const size_t tiles = (size_t)tiles_x * tiles_y, N = (size_t)width * height;
+  GeomBuf G = carve_geom(const_cast<char*>(geom_buffer), P, V);
+  BinBuf B = carve_bin(const_cast<char*>(binning_buffer), (size_t)R);
+  ImgBuf I = carve_img(const_cast<char*>(image_buffer), V, N, tiles);
+  Header hv;
+  IGS_CUDA_CHECK(cudaMemcpyAsync(&hv, G.hdr, sizeof(Header), cudaMemcpyDeviceToHost, s));
+  IGS_CUDA_CHECK(cudaStreamSynchronize(s));
+  if (hv.magic != IGS_MAGIC || hv.R != (uint32_t)R || hv.P != (uint32_t)P || hv.V != (uint32_t)V) { set_error("buffer mismatch in count"); return IGS_ERR_INVALID; }
+  BlendFwdParams bp;
+  memset(&bp, 0, sizeof(bp));
+  bp.W = width; bp.H = height; bp.tiles_x = tiles_x; bp.tiles_y = tiles_y; bp.focal_x = 1.0f; bp.focal_y = 1.0f;
+  bp.ranges = I.ranges; bp.point_list = B.point_list; bp.head = G.head; bp.tail = G.tail;
+  launch_blend_count(bp, V, counts, s);
+  IGS_CUDA_CHECK(cudaGetLastError());
+  return IGS_OK;
+}
+
 int igs_activate_forward(int P, const float* log_scales, const float* raw_rot, const float* opacity_logit, float* scales,
                          float* rotations, float* opacities, void* stream) {
   if (P < 0) { set_error("bad argument"); return IGS_ERR_INVALID; }
@@ -549,12 +607,12 @@ int igs_activate_backward(int P, const float* scales, const float* raw_rot, cons
   return IGS_OK;
 }
 
-int igs_densify_stats(int P, int V, const float* dL_dmeans2D, const int* radii, float* grad_accum, float* denom,
-                      float* max_radii2D, void* stream) {
+int igs_densify_stats(int P, int V, const float* dL_dmeans2D, const int* radii, float grad_scale, float* grad_accum,
+                      float* denom, float* max_radii2D, void* stream) {
   if (P < 0 || V < 0) { set_error("bad argument"); return IGS_ERR_INVALID; }
   if (P == 0 || V == 0) return IGS_OK;
   if (!dL_dmeans2D || !radii || !grad_accum || !denom || !max_radii2D) { set_error("null pointer"); return IGS_ERR_INVALID; }
-  launch_densify_stats(P, V, dL_dmeans2D, radii, grad_accum, denom, max_radii2D, (cudaStream_t)stream);
+  launch_densify_stats(P, V, dL_dmeans2D, radii, grad_scale, grad_accum, denom, max_radii2D, (cudaStream_t)stream);
   IGS_CUDA_CHECK(cudaGetLastError());
   return IGS_OK;
 }

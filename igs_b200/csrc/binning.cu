@@ -120,6 +120,14 @@ void launch_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint32_t
 // ---------------------------------------------------------------------------------------------
 // Stable LSD radix sort, 8-bit digits, 256 threads x 16 keys per block.
 // ---------------------------------------------------------------------------------------------
+// Effective element count of a launch that was sized for a CAPACITY: when n_dev is given, the true count lives in device
+// memory (the instance total written by the scan, never read back by the host in capacity mode) and is clamped to n.
+__device__ __forceinline__ size_t effective_n(size_t n, const uint32_t* __restrict__ n_dev) {
+  if (n_dev == nullptr) return n;
+  const size_t t = (size_t)*n_dev;
+  return t < n ? t : n;
+}
+
 template <typename K>
 __device__ __forceinline__ uint32_t digit_of(K key, int shift, uint32_t mask) {
   return (uint32_t)(key >> shift) & mask;
@@ -144,10 +152,10 @@ __device__ __forceinline__ void radix_hist_body(const K* __restrict__ keys, size
 
 template <typename K, int BITS>
 __global__ void __launch_bounds__(IGS_SORT_THREADS)
-radix_hist_kernel(const K* __restrict__ keys, size_t n, int shift, uint32_t mask, uint32_t* __restrict__ hist,
-                  unsigned nblocks) {
+radix_hist_kernel(const K* __restrict__ keys, size_t n, const uint32_t* __restrict__ n_dev, int shift, uint32_t mask,
+                  uint32_t* __restrict__ hist, unsigned nblocks) {
   __shared__ uint32_t h[1 << BITS];
-  radix_hist_body<K, BITS>(keys, n, shift, mask, hist, nblocks, blockIdx.x, h);
+  radix_hist_body<K, BITS>(keys, effective_n(n, n_dev), shift, mask, hist, nblocks, blockIdx.x, h);
 }
 
 // Each warp ranks a contiguous chunk of 512 keys in 16 rounds of 32 consecutive keys, so that the rank order equals
@@ -261,7 +269,8 @@ __device__ __forceinline__ void radix_scatter_body(const K* __restrict__ keys_in
     }
   }
   __syncthreads();
-  const uint32_t nvalid = (uint32_t)(n - bbase < (size_t)IGS_SORT_TILE ? n - bbase : (size_t)IGS_SORT_TILE);
+  // (a tile that lies entirely past the element count exists only in capacity mode: it moves nothing)
+  const uint32_t nvalid = bbase >= n ? 0u : (uint32_t)(n - bbase < (size_t)IGS_SORT_TILE ? n - bbase : (size_t)IGS_SORT_TILE);
   for (uint32_t j = threadIdx.x; j < nvalid; j += IGS_SORT_THREADS) {
     const K k = s_key[j];
     const uint32_t pos = dig_global[digit_of<K>(k, shift, mask)] + j;
@@ -273,10 +282,11 @@ __device__ __forceinline__ void radix_scatter_body(const K* __restrict__ keys_in
 template <typename K, int BITS>
 __global__ void __launch_bounds__(IGS_SORT_THREADS, sizeof(K) == 4 ? 4 : 3)
 radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__ vals_in, K* __restrict__ keys_out,
-                     uint32_t* __restrict__ vals_out, size_t n, int shift, uint32_t mask,
+                     uint32_t* __restrict__ vals_out, size_t n, const uint32_t* __restrict__ n_dev, int shift, uint32_t mask,
                      const uint32_t* __restrict__ hist_scanned, unsigned nblocks) {
   extern __shared__ __align__(16) unsigned char sort_smem[];
-  radix_scatter_body<K, BITS>(keys_in, vals_in, keys_out, vals_out, n, shift, mask, hist_scanned, nblocks, blockIdx.x, sort_smem);
+  radix_scatter_body<K, BITS>(keys_in, vals_in, keys_out, vals_out, effective_n(n, n_dev), shift, mask, hist_scanned, nblocks,
+                              blockIdx.x, sort_smem);
 }
 
 // The whole sort in ONE cooperative launch: persistent CTAs loop over the tiles of each phase (histogram, the two scan
@@ -285,8 +295,10 @@ radix_scatter_kernel(const K* __restrict__ keys_in, const uint32_t* __restrict__
 // the 2.5 views a rank renders at N = 8) those launches, not the kernels, were the cost of binning.
 template <typename K, int BITS>
 __global__ void __launch_bounds__(IGS_SORT_THREADS, sizeof(K) == 4 ? 4 : 3)
-radix_sort_coop_kernel(K* k0, K* k1, uint32_t* v0, uint32_t* v1, size_t n, int end_bit, uint32_t* hist, unsigned ntiles) {
+radix_sort_coop_kernel(K* k0, K* k1, uint32_t* v0, uint32_t* v1, size_t n_cap, const uint32_t* n_dev, int end_bit,
+                       uint32_t* hist, unsigned ntiles) {
   constexpr int NB = 1 << BITS;
+  const size_t n = effective_n(n_cap, n_dev);
   extern __shared__ __align__(16) unsigned char sort_smem[];
   uint32_t* sm32 = reinterpret_cast<uint32_t*>(sort_smem);
   cooperative_groups::grid_group grid = cooperative_groups::this_grid();
@@ -333,7 +345,8 @@ static int coop_capacity() {   // co-resident CTAs of the cooperative sort kerne
 }
 
 template <typename K, int BITS>
-static int radix_sort_passes(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint32_t* hist, cudaStream_t s) {
+static int radix_sort_passes(K* keys[2], uint32_t* vals[2], size_t n, const uint32_t* n_dev, int end_bit, uint32_t* hist,
+                             cudaStream_t s) {
   constexpr int NB = 1 << BITS;
   unsigned nb = (unsigned)sort_blocks(n);
   const int passes = (end_bit + BITS - 1) / BITS;
@@ -346,7 +359,7 @@ static int radix_sort_passes(K* keys[2], uint32_t* vals[2], size_t n, int end_bi
     unsigned grid = nb;
     K* k0 = keys[0]; K* k1 = keys[1];
     uint32_t* v0 = vals[0]; uint32_t* v1 = vals[1];
-    void* args[] = {&k0, &k1, &v0, &v1, &n, &end_bit, &hist, &nb};
+    void* args[] = {&k0, &k1, &v0, &v1, &n, &n_dev, &end_bit, &hist, &nb};
     cudaError_t e = cudaLaunchCooperativeKernel((const void*)radix_sort_coop_kernel<K, BITS>, dim3(grid), dim3(IGS_SORT_THREADS),
                                                 args, ScatterSmem<K, BITS>::bytes, s);
     if (e == cudaSuccess) {
@@ -363,11 +376,11 @@ static int radix_sort_passes(K* keys[2], uint32_t* vals[2], size_t n, int end_bi
     int bits = end_bit - shift < BITS ? end_bit - shift : BITS;
     uint32_t mask = (1u << bits) - 1u;
     count_launch(2);
-    radix_hist_kernel<K, BITS><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], n, shift, mask, hist, nb);
+    radix_hist_kernel<K, BITS><<<nb, IGS_SORT_THREADS, 0, s>>>(keys[cur], n, n_dev, shift, mask, hist, nb);
     // in-place exclusive scan over the bin-major histogram (its block sums live behind the histogram)
     launch_exclusive_scan(hist, hist, (size_t)NB * nb, hist + (size_t)NB * nb, nullptr, s);
     radix_scatter_kernel<K, BITS><<<nb, IGS_SORT_THREADS, ScatterSmem<K, BITS>::bytes, s>>>(
-        keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, shift, mask, hist, nb);
+        keys[cur], vals[cur], keys[cur ^ 1], vals[cur ^ 1], n, n_dev, shift, mask, hist, nb);
     cur ^= 1;
   }
   return cur;
@@ -375,19 +388,19 @@ static int radix_sort_passes(K* keys[2], uint32_t* vals[2], size_t n, int end_bi
 
 // Sorts n (key,value) pairs on key bits [0, end_bit).  Buffers ping-pong; returns the index (0/1)
 // of the buffer pair that holds the sorted result.  9-bit digits are used when they save a pass
-// (e.g. 17 tile-id bits at C3: 2 passes instead of 3).
+// (e.g. 17 tile-id bits at C3: 2 passes instead of 3).  n_dev (optional): the launches are sized for n, the number of
+// pairs actually present is min(*n_dev, n), read on the device (capacity mode: no host read-back of the count).
 template <typename K>
 int radix_sort_pairs(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint32_t* hist,
-                     uint32_t* scan_tmp_unused, cudaStream_t s) {
-  (void)scan_tmp_unused;
+                     const uint32_t* n_dev, cudaStream_t s) {
   if (n == 0) return 0;
   const int p8 = (end_bit + 7) / 8, p9 = (end_bit + 8) / 9;
-  if (p9 < p8) return radix_sort_passes<K, 9>(keys, vals, n, end_bit, hist, s);
-  return radix_sort_passes<K, 8>(keys, vals, n, end_bit, hist, s);
+  if (p9 < p8) return radix_sort_passes<K, 9>(keys, vals, n, n_dev, end_bit, hist, s);
+  return radix_sort_passes<K, 8>(keys, vals, n, n_dev, end_bit, hist, s);
 }
 
-template int radix_sort_pairs<uint64_t>(uint64_t* keys[2], uint32_t* vals[2], size_t, int, uint32_t*, uint32_t*, cudaStream_t);
-template int radix_sort_pairs<uint32_t>(uint32_t* keys[2], uint32_t* vals[2], size_t, int, uint32_t*, uint32_t*, cudaStream_t);
+template int radix_sort_pairs<uint64_t>(uint64_t* keys[2], uint32_t* vals[2], size_t, int, uint32_t*, const uint32_t*, cudaStream_t);
+template int radix_sort_pairs<uint32_t>(uint32_t* keys[2], uint32_t* vals[2], size_t, int, uint32_t*, const uint32_t*, cudaStream_t);
 
 // ---------------------------------------------------------------------------------------------
 // After sort A: tiles in depth order + inverse permutation
@@ -432,7 +445,7 @@ emit_instances_kernel(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Cam
                       const uint32_t* __restrict__ sorted_gid,
                       const uint32_t* __restrict__ inst_off, const SplatHead* __restrict__ head,
                       const int* __restrict__ radii, uint32_t* __restrict__ tkey, uint32_t* __restrict__ tval,
-                      uint32_t* __restrict__ inst_gid) {
+                      uint32_t* __restrict__ inst_gid, uint32_t capacity) {
   const size_t wid = ((size_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const uint32_t lane = lane_id();
   const size_t i0 = wid * 32;
@@ -470,7 +483,7 @@ emit_instances_kernel(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Cam
     const uint32_t o_xy = __shfl_sync(0xffffffffu, xy, lo);
     const uint32_t o_w = __shfl_sync(0xffffffffu, width, lo);
     const uint32_t o_tb = __shfl_sync(0xffffffffu, tbase, lo);
-    if (e < end) {
+    if (e < end && e < capacity) {   // capacity mode: instances past the binning buffer are dropped (overflow is flagged)
       const uint32_t local = e - o_off;
       const uint32_t ry = local / o_w, rx = local - ry * o_w;
       tkey[e] = o_tb + ((o_xy >> 16) + ry) * (uint32_t)tiles_x + (o_xy & 0xffffu) + rx;
@@ -483,12 +496,12 @@ emit_instances_kernel(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Cam
 void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Camera* cams,
                            const uint32_t* sorted_gid,
                            const uint32_t* inst_off, const SplatHead* head, const int* radii, uint32_t* tkey,
-                           uint32_t* tval, uint32_t* inst_gid, cudaStream_t s) {
+                           uint32_t* tval, uint32_t* inst_gid, uint32_t capacity, cudaStream_t s) {
   if (VP == 0) return;
   unsigned nb = (unsigned)((((VP + 31) / 32) * 32 + 255) / 256);   // one warp per 32 Gaussians, 8 warps per block
   count_launch();
   emit_instances_kernel<<<nb, 256, 0, s>>>(VP, P, tiles_x, tiles_y, cams, sorted_gid, inst_off, head, radii, tkey, tval,
-                                           inst_gid);
+                                           inst_gid, capacity);
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -504,9 +517,10 @@ __device__ __forceinline__ void mark_boundary(uint2* __restrict__ ranges, uint32
 }
 
 __global__ void __launch_bounds__(256)
-finalize_bins_kernel(uint32_t R, const uint32_t* __restrict__ tkey, const uint32_t* __restrict__ point_e,
-                     const uint32_t* __restrict__ inst_gid, uint32_t* __restrict__ point_list,
-                     uint2* __restrict__ ranges) {
+finalize_bins_kernel(uint32_t R_cap, const uint32_t* __restrict__ n_dev, const uint32_t* __restrict__ tkey,
+                     const uint32_t* __restrict__ point_e, const uint32_t* __restrict__ inst_gid,
+                     uint32_t* __restrict__ point_list, uint2* __restrict__ ranges) {
+  const uint32_t R = (uint32_t)effective_n(R_cap, n_dev);
   const uint32_t j0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4u;
   if (j0 >= R) return;
   if (j0 + 4 <= R) {
@@ -531,12 +545,12 @@ finalize_bins_kernel(uint32_t R, const uint32_t* __restrict__ tkey, const uint32
   }
 }
 
-void launch_finalize_bins(uint32_t R, const uint32_t* tkey, const uint32_t* point_e, const uint32_t* inst_gid,
-                          uint32_t* point_list, uint2* ranges, cudaStream_t s) {
+void launch_finalize_bins(uint32_t R, const uint32_t* n_dev, const uint32_t* tkey, const uint32_t* point_e,
+                          const uint32_t* inst_gid, uint32_t* point_list, uint2* ranges, cudaStream_t s) {
   if (R == 0) return;
   count_launch();
   const uint32_t threads = (R + 3) / 4;
-  finalize_bins_kernel<<<(threads + 255) / 256, 256, 0, s>>>(R, tkey, point_e, inst_gid, point_list, ranges);
+  finalize_bins_kernel<<<(threads + 255) / 256, 256, 0, s>>>(R, n_dev, tkey, point_e, inst_gid, point_list, ranges);
 }
 
 // Decode helper for tests: 64-bit reference-style keys in sorted order.

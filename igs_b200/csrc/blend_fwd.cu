@@ -21,7 +21,9 @@ namespace igs {
 
 #define BLEND_BATCH 256
 
-template <bool COORD, bool DEPTH, bool NORMAL, int MINB>
+// COUNT = true is the instrumentation build behind igs_count_blend_pairs: the same traversal, no image is written, and
+// the work counters of bench.py's roofline are accumulated instead.
+template <bool COORD, bool DEPTH, bool NORMAL, int MINB, bool COUNT = false>
 __global__ void __launch_bounds__(256, MINB)
 blend_fwd_kernel(BlendFwdParams p) {
   constexpr bool GEO = COORD || DEPTH || NORMAL;
@@ -57,6 +59,7 @@ blend_fwd_kernel(BlendFwdParams p) {
 
   const uint2 range = p.ranges[gt];
   int done = inside ? 0 : 1;
+  uint32_t n_hits = 0, n_eval = 0, n_contr = 0, n_staged = 0;  // COUNT only
 
   float T = 1.0f;
   uint32_t last_contributor = 0, max_contributor = 0xFFFFFFFFu;
@@ -78,6 +81,7 @@ blend_fwd_kernel(BlendFwdParams p) {
     float ex = 0, ey = 0, tau = 0;
     uint32_t gid = 0;
     if (j < range.y) {
+      if constexpr (COUNT) n_staged++;
       gid = p.point_list[j];
       ha = p.head[gid].a;
       hb = p.head[gid].b;
@@ -141,6 +145,11 @@ blend_fwd_kernel(BlendFwdParams p) {
           unpack2(mul2(pack2(alpha, fsub(1.0f, alpha)), pack2(T, T)), aT, test_T);  // fmul(alpha, T), fmul(T, 1 - alpha)
           const bool cand = (done == 0) && !(power > 0.0f) && !(alpha < 1.0f / 255.0f);
           const bool term = cand && (test_T < 0.0001f);
+          if constexpr (COUNT) {
+            n_hits += (lane == 0);
+            n_eval += (done == 0) && !(power > 0.0f);
+            n_contr += cand && !term;
+          }
           if (term) done = 1;
           if (!cand || term) continue;
           const float4 cq = lds128<BLEND_BATCH * 32>(ak);  // {blue, 1, position, tau}
@@ -179,6 +188,22 @@ blend_fwd_kernel(BlendFwdParams p) {
     }
   }
 
+  if constexpr (COUNT) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      n_hits += __shfl_xor_sync(0xffffffffu, n_hits, o);
+      n_eval += __shfl_xor_sync(0xffffffffu, n_eval, o);
+      n_contr += __shfl_xor_sync(0xffffffffu, n_contr, o);
+      n_staged += __shfl_xor_sync(0xffffffffu, n_staged, o);
+    }
+    if (lane == 0) {
+      atomicAdd(p.counters + 0, (unsigned long long)n_hits);
+      atomicAdd(p.counters + 1, (unsigned long long)n_eval);
+      atomicAdd(p.counters + 2, (unsigned long long)n_contr);
+      atomicAdd(p.counters + 3, (unsigned long long)n_staged);
+    }
+    return;
+  }
   float C0, C1, C2, weight, Co0, Co1, Co2, Depth, N0, N1;
   unpack2(C01, C0, C1);
   unpack2(C2w, C2, weight);
@@ -228,6 +253,15 @@ blend_fwd_kernel(BlendFwdParams p) {
       }
     }
   }
+}
+
+void launch_blend_count(const BlendFwdParams& p, int V, unsigned long long* counts, cudaStream_t s) {
+  int nblocks = V * p.tiles_x * p.tiles_y;
+  if (nblocks <= 0) return;
+  BlendFwdParams q = p;
+  q.counters = counts;
+  count_launch();
+  blend_fwd_kernel<false, false, false, 4, true><<<nblocks, 256, 0, s>>>(q);
 }
 
 void launch_blend_fwd(const BlendFwdParams& p, int V, bool coord, bool depth, cudaStream_t s) {

@@ -16,10 +16,10 @@
 namespace igs {
 
 // One step's densification statistics for all V views (the reference updates them once per single-view iteration):
-//   grad_accum[g] += |dL_dmeans2D[v][g].xy| and denom[g] += 1 for every view v that saw g (radii > 0),
+//   grad_accum[g] += grad_scale * |dL_dmeans2D[v][g].xy| and denom[g] += 1 for every view v that saw g (radii > 0),
 //   max_radii2D[g] = max(max_radii2D[g], radii[v][g]).
 __global__ void __launch_bounds__(256)
-densify_stats_kernel(int P, int V, const float* __restrict__ g2d, const int* __restrict__ radii,
+densify_stats_kernel(int P, int V, const float* __restrict__ g2d, const int* __restrict__ radii, float grad_scale,
                      float* __restrict__ grad_accum, float* __restrict__ denom, float* __restrict__ max_radii) {
   const int g = blockIdx.x * blockDim.x + threadIdx.x;
   if (g >= P) return;
@@ -29,7 +29,7 @@ densify_stats_kernel(int P, int V, const float* __restrict__ g2d, const int* __r
     const int r = radii[i];
     if (r > 0) {
       const float gx = g2d[3 * i], gy = g2d[3 * i + 1];
-      acc += sqrtf(gx * gx + gy * gy);   // torch.norm(grad[:, :2], dim=-1)
+      acc += grad_scale * sqrtf(gx * gx + gy * gy);   // torch.norm(grad[:, :2], dim=-1), on the per-view scale
       den += 1.0f;
       mr = fmaxf(mr, (float)r);
     }
@@ -91,11 +91,11 @@ densify_gather_kernel(DensifyGatherParams p) {
   p.v_new[in] = kind == 0 ? p.v_old[io] : 0.0f;
 }
 
-void launch_densify_stats(int P, int V, const float* g2d, const int* radii, float* grad_accum, float* denom,
-                          float* max_radii, cudaStream_t s) {
+void launch_densify_stats(int P, int V, const float* g2d, const int* radii, float grad_scale, float* grad_accum,
+                          float* denom, float* max_radii, cudaStream_t s) {
   if (P <= 0 || V <= 0) return;
   count_launch();
-  densify_stats_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, V, g2d, radii, grad_accum, denom, max_radii);
+  densify_stats_kernel<<<(P + 255) / 256, 256, 0, s>>>(P, V, g2d, radii, grad_scale, grad_accum, denom, max_radii);
 }
 
 void launch_densify_gather(int P_old, int P_new, const int* src, const uint8_t* kind, const float* samples,

@@ -34,6 +34,7 @@ struct BlendFwdParams {
   float* accum_coord;
   float* accum_depth;
   float* normal_length;
+  unsigned long long* counters;  // instrumentation build only (igs_count_blend_pairs)
 };
 
 struct BlendBwdParams {
@@ -65,6 +66,7 @@ struct BlendBwdParams {
 struct GatherBwdParams {
   int P, V, W, H;
   int ns;  // floats per record (16 or 32)
+  uint32_t capacity;  // emission slots the record buffer holds (R)
   float focal_x, focal_y, tan_fovx, tan_fovy, kernel_size;
   const float* means3D;
   const Camera* cams;
@@ -110,16 +112,16 @@ void launch_mark_visible(int P, const float* means3D, const float* view, uint8_t
 void launch_exclusive_scan(const uint32_t* in, uint32_t* out, size_t n, uint32_t* block_sums, uint32_t* total,
                            cudaStream_t s);
 template <typename K>
-int radix_sort_pairs(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint32_t* hist, uint32_t* unused,
+int radix_sort_pairs(K* keys[2], uint32_t* vals[2], size_t n, int end_bit, uint32_t* hist, const uint32_t* n_dev,
                      cudaStream_t s);
 void launch_gather_rank(size_t VP, const uint32_t* sorted_gid, const uint32_t* tiles, uint32_t* tiles_sorted,
                         uint32_t* rank, cudaStream_t s);
 void launch_emit_instances(size_t VP, uint32_t P, int tiles_x, int tiles_y, const Camera* cams,
                            const uint32_t* sorted_gid,
                            const uint32_t* inst_off, const SplatHead* head, const int* radii, uint32_t* tkey,
-                           uint32_t* tval, uint32_t* inst_gid, cudaStream_t s);
-void launch_finalize_bins(uint32_t R, const uint32_t* tkey, const uint32_t* point_e, const uint32_t* inst_gid,
-                          uint32_t* point_list, uint2* ranges, cudaStream_t s);
+                           uint32_t* tval, uint32_t* inst_gid, uint32_t capacity, cudaStream_t s);
+void launch_finalize_bins(uint32_t R, const uint32_t* n_dev, const uint32_t* tkey, const uint32_t* point_e,
+                          const uint32_t* inst_gid, uint32_t* point_list, uint2* ranges, cudaStream_t s);
 void launch_decode_keys(uint32_t R, uint32_t tiles_per_view, uint32_t P, const uint32_t* tkey,
                         const uint32_t* point_list, const float* depth, uint64_t* keys, uint32_t* plist_local,
                         cudaStream_t s);
@@ -139,13 +141,18 @@ void launch_activate_fwd(int P, const float* log_scales, const float* raw_rot, c
 void launch_activate_bwd(int P, const float* scales, const float* raw_rot, const float* opac, const float* dL_dscales,
                          const float* dL_drot, const float* dL_dopac, float* dL_dlog_scales, float* dL_draw_rot,
                          float* dL_dlogit, cudaStream_t s);
-void launch_densify_stats(int P, int V, const float* g2d, const int* radii, float* grad_accum, float* denom,
-                          float* max_radii, cudaStream_t s);
+void launch_densify_stats(int P, int V, const float* g2d, const int* radii, float grad_scale, float* grad_accum,
+                          float* denom, float* max_radii, cudaStream_t s);
 void launch_densify_gather(int P_old, int P_new, const int* src, const uint8_t* kind, const float* samples,
                            float split_div, const size_t* off_old, const size_t* off_new, const float* param_old,
                            const float* m_old, const float* v_old, float* param_new, float* m_new, float* v_new,
                            cudaStream_t s);
 void launch_adam_groups(float* p, const float* g, float* m, float* v, int ngroups, const size_t* sizes,
                         const float* step_sizes, float b1, float b2, float eps, float inv_sqrt_bc2, cudaStream_t s);
+// guarded / device-step variant: lrs instead of step sizes, bias corrections computed on the device from *step_dev
+void launch_adam_groups_guarded(float* p, const float* g, float* m, float* v, int ngroups, const size_t* sizes,
+                                const float* lrs, float b1, float b2, float eps, int step, const unsigned int* skip,
+                                int* step_dev, cudaStream_t s);
+void launch_blend_count(const BlendFwdParams& p, int V, unsigned long long* counts, cudaStream_t s);
 
 }  // namespace igs

@@ -33,15 +33,16 @@ namespace igs {
 template <int NS>
 __global__ void __launch_bounds__(256)
 sum_records_kernel(size_t VP, const uint32_t* __restrict__ inst_off, const float* __restrict__ grec,
-                   float* __restrict__ sums) {
+                   float* __restrict__ sums, uint32_t capacity) {
   constexpr int LANES = NS / 4;                // 16-byte parts per record
   constexpr int PARTS = NS == 16 ? 3 : 7;      // parts that carry values (10 / 25 floats)
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t pos = t / LANES;
   const int part = (int)(t % LANES);
   if (pos >= VP || part >= PARTS) return;
-  const uint32_t off = inst_off[pos];
-  const uint32_t n = inst_off[pos + 1] - off;
+  // (capacity mode: records exist for emission slots < capacity only; an overflowing call is discarded by the caller)
+  const uint32_t off = min(inst_off[pos], capacity);
+  const uint32_t n = min(inst_off[pos + 1], capacity) - off;
   const float4* r = reinterpret_cast<const float4*>(grec) + (size_t)off * LANES + part;
   float4 acc = make_float4(0, 0, 0, 0);
   uint32_t k = 0;
@@ -563,8 +564,8 @@ void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s) {
   if (p.P <= 0) return;
   const size_t VP = (size_t)p.V * p.P;
   count_launch(2);
-  if (p.ns == 16) sum_records_kernel<16><<<(unsigned)((VP * 4 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums);
-  else sum_records_kernel<32><<<(unsigned)((VP * 8 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums);
+  if (p.ns == 16) sum_records_kernel<16><<<(unsigned)((VP * 4 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums, p.capacity);
+  else sum_records_kernel<32><<<(unsigned)((VP * 8 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums, p.capacity);
   gather_bwd_kernel<<<(unsigned)((VP + 127) / 128), 128, 0, s>>>(p);
 }
 

@@ -52,7 +52,8 @@ FwdRet forward_impl(const torch::Tensor& background, const torch::Tensor& means3
                     const torch::Tensor& projmatrix, float tan_fovx, float tan_fovy, float kernel_size, int H, int W,
                     const torch::Tensor& sh, int degree, const torch::Tensor& campos, bool prefiltered,
                     bool require_coord, bool require_depth, bool debug, int V, bool batched,
-                    const torch::Tensor& tile_rows = torch::Tensor()) {
+                    const torch::Tensor& tile_rows = torch::Tensor(), int64_t instance_capacity = 0,
+                    const torch::Tensor& status = torch::Tensor()) {
   if (means3D.ndimension() != 2 || means3D.size(1) != 3) {
     AT_ERROR("means3D must have dimensions (num_points, 3)");
   }
@@ -115,6 +116,13 @@ FwdRet forward_impl(const torch::Tensor& background, const torch::Tensor& means3
                   "tile_rows must be a CUDA int32 tensor [V,2]");
       tr = tile_rows.contiguous();
       a.tile_rows = tr.data_ptr<int>();
+    }
+    TORCH_CHECK(instance_capacity >= 0 && instance_capacity <= 0x7FFFFFFF, "instance_capacity out of range");
+    a.instance_capacity = (int)instance_capacity;
+    if (status.defined() && status.numel() != 0) {
+      TORCH_CHECK(status.is_cuda() && status.scalar_type() == torch::kInt32 && status.numel() >= 2 && status.is_contiguous(),
+                  "status must be a contiguous CUDA int32 tensor with 2 elements");
+      a.status = reinterpret_cast<unsigned int*>(status.data_ptr<int>());
     }
     TORCH_CHECK(a.background && a.opacities && a.viewmatrix && a.projmatrix && a.cam_pos, "missing required CUDA input");
     TORCH_CHECK(vm.numel() == (int64_t)V * 16 && pm.numel() == (int64_t)V * 16 && cp.numel() == (int64_t)V * 3,
@@ -259,13 +267,15 @@ FwdRet RasterizeViewsCUDA(const torch::Tensor& background, const torch::Tensor& 
                           const float tan_fovy, const float kernel_size, const int image_height, const int image_width,
                           const torch::Tensor& sh, const int degree, const torch::Tensor& campos,
                           const bool prefiltered, const bool require_coord, const bool require_depth, const bool debug,
-                          const c10::optional<torch::Tensor>& tile_rows_opt) {
+                          const c10::optional<torch::Tensor>& tile_rows_opt, int64_t instance_capacity,
+                          const c10::optional<torch::Tensor>& status_opt) {
   const torch::Tensor tile_rows = tile_rows_opt.has_value() ? *tile_rows_opt : torch::Tensor();
+  const torch::Tensor status = status_opt.has_value() ? *status_opt : torch::Tensor();
   TORCH_CHECK(viewmatrices.dim() == 3, "viewmatrices must be [V,4,4]");
   return forward_impl(background, means3D, colors, opacity, scales, rotations, scale_modifier, cov3D_precomp,
                       viewmatrices, projmatrices, tan_fovx, tan_fovy, kernel_size, image_height, image_width, sh, degree,
                       campos, prefiltered, require_coord, require_depth, debug, (int)viewmatrices.size(0), true,
-                      tile_rows);
+                      tile_rows, instance_capacity, status);
 }
 
 BwdRet RasterizeViewsBackwardCUDA(
@@ -316,6 +326,21 @@ std::vector<torch::Tensor> DecodeBuffers(int P, int V, int R, int H, int W, cons
                            (void*)at::cuda::getCurrentCUDAStream().stream()),
         "decode_buffers");
   return {keys, plist, ranges, ncontrib, tiles_t, depths, means2D, conic, rgb, cov3D, vp, cpl, rp, ts, nrm};
+}
+
+// Work counters of the blend traversal for bench.py's roofline: int64 [4] = {block-level hits, E' evaluated pixel pairs,
+// C contributing pixel pairs, instances staged} (igs_count_blend_pairs).
+torch::Tensor CountBlendPairs(int P, int V, int R, int H, int W, const torch::Tensor& geomBuffer,
+                              const torch::Tensor& binningBuffer, const torch::Tensor& imageBuffer) {
+  const c10::cuda::CUDAGuard guard(geomBuffer.device());
+  torch::Tensor counts = torch::zeros({4}, torch::TensorOptions().dtype(torch::kInt64).device(geomBuffer.device()));
+  check(igs_count_blend_pairs(P, V, R, W, H, reinterpret_cast<const char*>(geomBuffer.data_ptr()),
+                              R > 0 ? reinterpret_cast<const char*>(binningBuffer.data_ptr()) : nullptr,
+                              reinterpret_cast<const char*>(imageBuffer.data_ptr()),
+                              reinterpret_cast<unsigned long long*>(counts.data_ptr<int64_t>()),
+                              (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "count_blend_pairs");
+  return counts;
 }
 
 void AdamStep(torch::Tensor& param, const torch::Tensor& grad, torch::Tensor& exp_avg, torch::Tensor& exp_avg_sq,
@@ -381,7 +406,8 @@ std::tuple<torch::Tensor, torch::Tensor, torch::Tensor, torch::Tensor> DepthNorm
 // Adam over the packed parameter record: one launch for all groups.
 void AdamStepGroups(torch::Tensor& param, const torch::Tensor& grad, torch::Tensor& exp_avg, torch::Tensor& exp_avg_sq,
                     const std::vector<int64_t>& sizes, const std::vector<double>& lrs, double beta1, double beta2,
-                    double eps, int64_t step) {
+                    double eps, int64_t step, const c10::optional<torch::Tensor>& skip_opt,
+                    const c10::optional<torch::Tensor>& step_dev_opt) {
   TORCH_CHECK(param.is_cuda() && grad.is_cuda() && exp_avg.is_cuda() && exp_avg_sq.is_cuda(), "Adam tensors must be CUDA");
   TORCH_CHECK(param.is_contiguous() && grad.is_contiguous() && exp_avg.is_contiguous() && exp_avg_sq.is_contiguous(),
               "Adam tensors must be contiguous");
@@ -394,6 +420,24 @@ void AdamStepGroups(torch::Tensor& param, const torch::Tensor& grad, torch::Tens
   TORCH_CHECK(total == param.numel() && total == grad.numel() && total == exp_avg.numel() && total == exp_avg_sq.numel(),
               "group sizes must add up to the buffer size");
   const c10::cuda::CUDAGuard guard(param.device());
+  if (skip_opt.has_value() || step_dev_opt.has_value()) {
+    const unsigned int* skip = nullptr;
+    int* step_dev = nullptr;
+    if (skip_opt.has_value()) {
+      TORCH_CHECK(skip_opt->is_cuda() && skip_opt->scalar_type() == torch::kInt32 && skip_opt->numel() >= 1, "skip must be a CUDA int32 tensor");
+      skip = reinterpret_cast<const unsigned int*>(skip_opt->data_ptr<int>());
+    }
+    if (step_dev_opt.has_value()) {
+      TORCH_CHECK(step_dev_opt->is_cuda() && step_dev_opt->scalar_type() == torch::kInt32 && step_dev_opt->numel() == 1, "step_dev must be a CUDA int32 scalar");
+      step_dev = step_dev_opt->data_ptr<int>();
+    }
+    check(igs_adam_step_groups_guarded(param.data_ptr<float>(), grad.data_ptr<float>(), exp_avg.data_ptr<float>(),
+                                       exp_avg_sq.data_ptr<float>(), (int)sz.size(), sz.data(), lr.data(), (float)beta1,
+                                       (float)beta2, (float)eps, (int)step, skip, step_dev,
+                                       (void*)at::cuda::getCurrentCUDAStream().stream()),
+          "adam_step_groups_guarded");
+    return;
+  }
   check(igs_adam_step_groups(param.data_ptr<float>(), grad.data_ptr<float>(), exp_avg.data_ptr<float>(),
                              exp_avg_sq.data_ptr<float>(), (int)sz.size(), sz.data(), lr.data(), (float)beta1,
                              (float)beta2, (float)eps, (int)step, (void*)at::cuda::getCurrentCUDAStream().stream()),
@@ -441,15 +485,18 @@ std::tuple<torch::Tensor, torch::Tensor, torch::Tensor> ActivateBackward(
 // (xyz, rotation, shs, opacity, scaling) inside them.  Returns (loss_sum/total_views [device scalar],
 // num_rendered, radii [V,P], dL_dmeans2D [V,P,3]).
 // Mirrors infer_batch.py:279-324 for V views at once (see igs_b200/refine.py).
-std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor> RefineGrad(
+std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor, torch::Tensor> RefineGrad(
     const torch::Tensor& flat, torch::Tensor& grad, const std::vector<int64_t>& offs, int64_t P64,
     const torch::Tensor& background, const torch::Tensor& viewmatrices, const torch::Tensor& projmatrices,
     const torch::Tensor& campos, double tan_fovx, double tan_fovy, double kernel_size, double scale_modifier, int H,
     int W, int degree, const torch::Tensor& gt, int64_t total_views, double lambda_l1, bool require_coord,
     bool require_depth, bool debug, const c10::optional<torch::Tensor>& tile_rows_opt,
-    const std::vector<int64_t>& loss_rows) {
+    const std::vector<int64_t>& loss_rows, int64_t instance_capacity, const c10::optional<torch::Tensor>& status_opt) {
   const torch::Tensor tile_rows = tile_rows_opt.has_value() ? *tile_rows_opt : torch::Tensor();
   TORCH_CHECK(flat.is_cuda() && grad.is_cuda(), "refine_grad needs CUDA tensors (there is no CPU path)");
+  // {true instance count, overflow flag} of this call's forward, on the device (capacity mode: see igs_forward_args)
+  torch::Tensor status = status_opt.has_value() ? *status_opt
+                                                : torch::zeros({2}, torch::TensorOptions().dtype(torch::kInt32).device(flat.device()));
   TORCH_CHECK(flat.is_contiguous() && grad.is_contiguous() && flat.numel() == grad.numel(), "flat/grad must be contiguous and equal-sized");
   TORCH_CHECK(flat.scalar_type() == torch::kFloat32 && grad.scalar_type() == torch::kFloat32, "float32 only");
   TORCH_CHECK(offs.size() == 5, "offs = (xyz, rotation, shs, opacity, scaling)");
@@ -476,7 +523,7 @@ std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor> RefineGrad(
   torch::Tensor none;
   FwdRet f = forward_impl(background, xyz, none, op, sc, rot, (float)scale_modifier, none, viewmatrices, projmatrices,
                           (float)tan_fovx, (float)tan_fovy, (float)kernel_size, H, W, shs, degree, campos, false,
-                          require_coord, require_depth, debug, V, true, tile_rows);
+                          require_coord, require_depth, debug, V, true, tile_rows, instance_capacity, status);
   const int rendered = std::get<0>(f);
   const torch::Tensor& color = std::get<1>(f);
   torch::Tensor loss = torch::zeros({}, flat.options());
@@ -505,11 +552,11 @@ std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor> RefineGrad(
                               slice(grad, 3, 1, {P, 1}).data_ptr<float>(), (void*)stream),
         "activate_backward");
   loss.mul_(gscale);
-  return std::make_tuple(loss, (int64_t)rendered, std::get<8>(f), std::get<0>(b));
+  return std::make_tuple(loss, (int64_t)rendered, std::get<8>(f), std::get<0>(b), status);
 }
 
 void DensifyStats(const torch::Tensor& g2d, const torch::Tensor& radii, torch::Tensor& grad_accum, torch::Tensor& denom,
-                  torch::Tensor& max_radii) {
+                  torch::Tensor& max_radii, double grad_scale) {
   TORCH_CHECK(g2d.is_cuda() && radii.is_cuda() && grad_accum.is_cuda(), "densify_stats needs CUDA tensors (there is no CPU path)");
   TORCH_CHECK(g2d.dim() == 3 && g2d.size(2) == 3 && radii.dim() == 2, "dL_dmeans2D must be [V,P,3] and radii [V,P]");
   TORCH_CHECK(radii.scalar_type() == torch::kInt32, "radii must be int32");
@@ -519,7 +566,7 @@ void DensifyStats(const torch::Tensor& g2d, const torch::Tensor& radii, torch::T
   TORCH_CHECK(grad_accum.is_contiguous() && denom.is_contiguous() && max_radii.is_contiguous(), "statistics must be contiguous");
   const c10::cuda::CUDAGuard guard(g2d.device());
   torch::Tensor g = g2d.contiguous(), r = radii.contiguous();
-  check(igs_densify_stats(P, V, fptr(g, "dL_dmeans2D"), r.data_ptr<int>(), grad_accum.data_ptr<float>(),
+  check(igs_densify_stats(P, V, fptr(g, "dL_dmeans2D"), r.data_ptr<int>(), (float)grad_scale, grad_accum.data_ptr<float>(),
                           denom.data_ptr<float>(), max_radii.data_ptr<float>(),
                           (void*)at::cuda::getCurrentCUDAStream().stream()),
         "densify_stats");
@@ -562,14 +609,20 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         pybind11::arg("tan_fovx"), pybind11::arg("tan_fovy"), pybind11::arg("kernel_size"), pybind11::arg("scale_modifier"),
         pybind11::arg("H"), pybind11::arg("W"), pybind11::arg("degree"), pybind11::arg("gt"), pybind11::arg("total_views"),
         pybind11::arg("lambda_l1"), pybind11::arg("require_coord"), pybind11::arg("require_depth"), pybind11::arg("debug"),
-        pybind11::arg("tile_rows") = pybind11::none(), pybind11::arg("loss_rows") = std::vector<int64_t>());
+        pybind11::arg("tile_rows") = pybind11::none(), pybind11::arg("loss_rows") = std::vector<int64_t>(),
+        pybind11::arg("instance_capacity") = 0, pybind11::arg("status") = pybind11::none());
   m.def("depth_normal_loss", &DepthNormalLoss, pybind11::arg("map0"), pybind11::arg("map1"), pybind11::arg("normal"),
         pybind11::arg("use_coord"), pybind11::arg("tan_fovx"), pybind11::arg("tan_fovy"), pybind11::arg("depth_ratio") = 0.6,
         pybind11::arg("grad_scale") = 1.0);
   m.def("activate_forward", &ActivateForward);
   m.def("activate_backward", &ActivateBackward);
-  m.def("adam_step_groups", &AdamStepGroups);
-  m.def("densify_stats", &DensifyStats);
+  m.def("adam_step_groups", &AdamStepGroups, pybind11::arg("param"), pybind11::arg("grad"), pybind11::arg("exp_avg"),
+        pybind11::arg("exp_avg_sq"), pybind11::arg("sizes"), pybind11::arg("lrs"), pybind11::arg("beta1"), pybind11::arg("beta2"),
+        pybind11::arg("eps"), pybind11::arg("step"), pybind11::arg("skip") = pybind11::none(),
+        pybind11::arg("step_dev") = pybind11::none());
+  m.def("count_blend_pairs", &CountBlendPairs);
+  m.def("densify_stats", &DensifyStats, pybind11::arg("dL_dmeans2D"), pybind11::arg("radii"), pybind11::arg("grad_accum"),
+        pybind11::arg("denom"), pybind11::arg("max_radii2D"), pybind11::arg("grad_scale") = 1.0);
   m.def("densify_gather", &DensifyGather);
   m.def("rasterize_gaussians", &RasterizeGaussiansCUDA);
   m.def("rasterize_gaussians_backward", &RasterizeGaussiansBackwardCUDA);
@@ -580,7 +633,8 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         pybind11::arg("tan_fovx"), pybind11::arg("tan_fovy"), pybind11::arg("kernel_size"), pybind11::arg("image_height"),
         pybind11::arg("image_width"), pybind11::arg("sh"), pybind11::arg("degree"), pybind11::arg("campos"),
         pybind11::arg("prefiltered"), pybind11::arg("require_coord"), pybind11::arg("require_depth"),
-        pybind11::arg("debug"), pybind11::arg("tile_rows") = pybind11::none());
+        pybind11::arg("debug"), pybind11::arg("tile_rows") = pybind11::none(), pybind11::arg("instance_capacity") = 0,
+        pybind11::arg("status") = pybind11::none());
   m.def("rasterize_views_backward", &RasterizeViewsBackwardCUDA);
   m.def("decode_buffers", &DecodeBuffers);
   m.def("adam_step", &AdamStep);

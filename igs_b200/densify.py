@@ -32,11 +32,16 @@ class DensifyStats:
         self.denom = torch.zeros(P, device=device)
         self.max_radii2D = torch.zeros(P, device=device)
 
-    def update(self, grad_means2D: torch.Tensor, radii: torch.Tensor) -> None:
+    def update(self, grad_means2D: torch.Tensor, radii: torch.Tensor, grad_scale: float = 1.0) -> None:
         """All V views of one step at once (the reference calls add_densification_stats once per single-view
-        iteration, infer_batch.py:312-313): grad_means2D [V,P,3], radii [V,P] int32."""
+        iteration, infer_batch.py:312-313): grad_means2D [V,P,3], radii [V,P] int32.
+
+        grad_scale: the reference accumulates the norm of the gradient of ONE view's undivided loss
+        (infer_batch.py:302-313); a step whose loss is the mean over `total_views` views hands in gradients that are
+        1/total_views of that, so the caller passes total_views and `densify_grad_threshold` keeps its meaning.  The
+        views must be whole images: a view rendered as several tile-row bands would be counted once per band."""
         from . import _C
-        _C.densify_stats(grad_means2D, radii, self.grad_accum, self.denom, self.max_radii2D)
+        _C.densify_stats(grad_means2D, radii, self.grad_accum, self.denom, self.max_radii2D, float(grad_scale))
 
     def all_reduce(self, group=None) -> None:
         """View-sharded refine: every rank saw only its views.  SUM the accumulators and MAX the radii over the
@@ -48,11 +53,11 @@ class DensifyStats:
         torch.distributed.all_reduce(self.denom, group=group)
         torch.distributed.all_reduce(self.max_radii2D, op=torch.distributed.ReduceOp.MAX, group=group)
 
-    def update_torch(self, grad_means2D: torch.Tensor, radii: torch.Tensor) -> None:
+    def update_torch(self, grad_means2D: torch.Tensor, radii: torch.Tensor, grad_scale: float = 1.0) -> None:
         """The same update with torch ops (restatement used by the tests)."""
         for v in range(radii.shape[0]):
             vis = radii[v] > 0
-            self.grad_accum[vis] += torch.norm(grad_means2D[v][vis, :2], dim=-1)
+            self.grad_accum[vis] += grad_scale * torch.norm(grad_means2D[v][vis, :2], dim=-1)
             self.denom[vis] += 1
             self.max_radii2D[vis] = torch.max(self.max_radii2D[vis], radii[v][vis].to(self.max_radii2D.dtype))
 
@@ -165,10 +170,14 @@ def apply_plan_torch(flat: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torc
 
 
 def densify_and_prune(state: RefineState, stats: DensifyStats, max_grad: float, min_opacity: float, extent: float,
-                      max_screen_size: Optional[float] = None, max_num: int = 150000, percent_dense: float = 0.01,
+                      max_screen_size: Optional[float] = None, max_num: int = 150000, percent_dense: float = 0.0,
                       control_max: bool = True, N: int = 2, generator: Optional[torch.Generator] = None) -> DensifyPlan:
     """GaussianModel.densify_and_prune on a RefineState: plans on [P] vectors, then ONE gather kernel rebuilds the
-    packed parameters and both Adam moments.  `state` and `stats` are updated in place; returns the plan."""
+    packed parameters and both Adam moments.  `state` and `stats` are updated in place; returns the plan.
+
+    percent_dense defaults to 0: that is its value on the refine path — GaussianModel.__init__ sets it to 0
+    (gaussian_model.py:84) and only training_setup(), which load_fromstream / infer_batch.py never call, changes it —
+    so the reference never clones there and splits every selected Gaussian."""
     from . import _C
     P_old = state.P
     plan = plan_densify(None, state.param("scaling"), state.param("opacity"), stats.grad_accum, stats.denom, max_grad,

@@ -53,6 +53,59 @@ class RefineState:
             self.flat[off:off + P * k].copy_(src[name].reshape(-1).to(self.device, non_blocking=True))
             off += P * k
         self.step = 0
+        # Capacity mode of the forward (no host read of the instance count, igs_forward_args.instance_capacity):
+        # off until enable_async_binning(); the high-water mark of the observed instance counts sizes the buffers.
+        self.async_binning = False
+        self.capacity_margin = 1.2
+        self._r_seen = {}             # number of local views -> largest instance count observed
+        self._pending = []            # (n_views, pinned host mirror of `status`, event) not yet looked at
+        self.overflows = 0            # forwards whose capacity was exceeded (their Adam step was skipped on the device)
+        self.status = torch.zeros(2, dtype=torch.int32, device=self.device)
+
+    # ---- capacity mode bookkeeping -------------------------------------------------------------------------------
+    def enable_async_binning(self, on: bool = True, margin: float = 1.2) -> None:
+        """From the next iteration on, forwards for a view count whose instance total has been seen once run without
+        the host round-trip (reference rasterizer_impl.cu:354): buffers are sized margin x the largest total seen, the
+        true total stays on the device, and an overflowing iteration turns its own Adam step into a no-op."""
+        self.async_binning = bool(on)
+        self.capacity_margin = float(margin)
+
+    def note_instances(self, n_views: int, R: int) -> None:
+        if R > self._r_seen.get(n_views, 0):
+            self._r_seen[n_views] = int(R)
+
+    def poll_status(self, wait: bool = False) -> None:
+        """Looks at the status words of finished capacity-mode iterations (no synchronisation unless `wait`)."""
+        keep = []
+        for n_views, host, ev in self._pending:
+            if wait:
+                ev.synchronize()
+            if ev.query():
+                self.note_instances(n_views, int(host[0]))
+                if int(host[1]) != 0:
+                    self.overflows += 1
+            else:
+                keep.append((n_views, host, ev))
+        self._pending = keep
+
+    def instance_capacity(self, n_views: int) -> int:
+        """0 = exact mode (count read back by the host); otherwise the capacity for a forward over n_views views."""
+        if not self.async_binning:
+            return 0
+        self.poll_status()
+        seen = self._r_seen.get(n_views, 0)
+        if seen <= 0:
+            return 0
+        return min(0x7FFFFFFF, (int(seen * self.capacity_margin) + 4095) // 4096 * 4096)
+
+    def track_status(self, n_views: int) -> None:
+        host = torch.empty(2, dtype=torch.int32, pin_memory=True)
+        host.copy_(self.status, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._pending.append((n_views, host, ev))
+        if len(self._pending) > 64:
+            self.poll_status(wait=True)
 
     def resize(self, P: int, flat: torch.Tensor, exp_avg: torch.Tensor, exp_avg_sq: torch.Tensor) -> None:
         """Adopts re-laid-out records of a new size (densify / prune, igs_b200/densify.py); Adam's step count is kept,
@@ -79,13 +132,14 @@ class RefineState:
         """H2D copy of all parameters from a (pinned) host buffer laid out like `self.flat`."""
         self.flat.copy_(host_flat, non_blocking=True)
 
-    def adam_step(self) -> None:
+    def adam_step(self, guarded: bool = False) -> None:
         """torch.optim.Adam(lr per group, betas=(0.9,0.999), eps=1e-15) — gaussian_model.py:348 — as one
-        fused kernel launch over all parameter groups (igs_adam_step_groups)."""
+        fused kernel launch over all parameter groups (igs_adam_step_groups).  guarded: the step becomes a no-op on
+        the device when this iteration's capacity-mode forward overflowed (self.status[1])."""
         self.step += 1
         _C.adam_step_groups(self.flat, self.grad, self.exp_avg, self.exp_avg_sq,
                             [self.P * k for _, k in GROUPS], [float(self.lrs[n]) for n, _ in GROUPS],
-                            0.9, 0.999, 1e-15, self.step)
+                            0.9, 0.999, 1e-15, self.step, skip=self.status[1:2] if guarded else None)
 
     def offsets(self):
         """Element offsets of (xyz, rotation, shs, opacity, scaling) in the packed record (refine_grad's `offs`)."""
@@ -186,15 +240,24 @@ def refine_iteration(state: RefineState, settings: MultiViewSettings, gt: torch.
     Vl = int(settings.viewmatrices.shape[0]) if settings is not None else 0
     if impl == "native" and loss_impl == "fused" and Vl > 0:
         s = settings
-        loss, R, radii, g2d = _C.refine_grad(
+        cap = state.instance_capacity(Vl)
+        loss, R, radii, g2d, _status = _C.refine_grad(
             state.flat, state.grad, state.offsets(), state.P, s.bg, s.viewmatrices, s.projmatrices, s.campos,
             float(s.tanfovx), float(s.tanfovy), float(s.kernel_size), float(s.scale_modifier), int(s.image_height),
             int(s.image_width), int(s.sh_degree), gt, int(total_views), float(lambda_l1), bool(s.require_coord),
             bool(s.require_depth), bool(s.debug), s.tile_rows,
-            list(s.loss_rows) if s.loss_rows else [])
+            list(s.loss_rows) if s.loss_rows else [], cap, state.status)
+        if cap == 0:
+            state.note_instances(Vl, int(R))     # exact mode: R is the true count
+        else:
+            state.track_status(Vl)               # capacity mode: the count is looked at later, without a sync
+        guarded = cap != 0
+        if guarded and group is not None and torch.distributed.get_world_size(group) > 1:
+            # one rank's overflow must skip the step on EVERY rank: fold the flag into the exchange
+            torch.distributed.all_reduce(state.status[1:2], op=torch.distributed.ReduceOp.MAX, group=group)
         loss = reduce_gradients(state.grad, loss, group)
         if do_step:
-            state.adam_step()
+            state.adam_step(guarded=guarded)
         return IterationResult(loss, int(R), radii, g2d)
     names = [n for n, _ in GROUPS]
     leaves = []
@@ -331,3 +394,80 @@ def settings_for_units(all_views: MultiViewSettings, units) -> MultiViewSettings
                               campos=all_views.campos[idx].contiguous(),
                               tile_rows=None if tr is None else tr.to(all_views.viewmatrices.device),
                               loss_rows=lr)
+
+
+# ------------------------------------------------------------------------------------------------
+# the single-rank iteration as ONE CUDA graph
+# ------------------------------------------------------------------------------------------------
+class GraphedIteration:
+    """activations -> forward -> loss -> backward -> Adam of one refine iteration captured in a CUDA graph.
+
+    Possible because the capacity mode of the forward needs no host read of the instance count (the reference's
+    blocking cudaMemcpy, rasterizer_impl.cu:354, is what makes its iteration un-capturable) and because the Adam step
+    count lives on the device (`igs_adam_step_groups_guarded`).  The cameras and the target image are static buffers:
+    `run(views, gt)` copies the iteration's inputs into them and replays.  An iteration whose instance count exceeds
+    the captured capacity skips its own Adam step on the device; `overflowed()` tells (it synchronises).
+
+    Single rank, fixed number of views per step, no tile-row bands.  Built by `stream.refine_keyframe(graph=True)`.
+    """
+
+    def __init__(self, state: RefineState, settings: MultiViewSettings, gt: torch.Tensor, total_views: int,
+                 capacity: int, lambda_l1: float = 0.8):
+        assert settings.tile_rows is None and not settings.loss_rows, "bands are not supported in the graphed iteration"
+        self.state = state
+        self.s = settings._replace(viewmatrices=settings.viewmatrices.clone(), projmatrices=settings.projmatrices.clone(),
+                                   campos=settings.campos.clone())
+        self.gt = gt.clone()
+        self.total_views = int(total_views)
+        self.capacity = int(capacity)
+        self.lambda_l1 = float(lambda_l1)
+        self.step_dev = torch.full((1,), state.step, dtype=torch.int32, device=state.device)
+        self.status = torch.zeros(2, dtype=torch.int32, device=state.device)
+        self.n_overflow = torch.zeros(1, dtype=torch.int32, device=state.device)
+        self.loss = torch.zeros((), device=state.device)
+        self.radii = None
+        self.g2d = None
+        self.replays = 0
+        side = torch.cuda.Stream(device=state.device)
+        side.wait_stream(torch.cuda.current_stream(state.device))
+        with torch.cuda.stream(side):           # warm-up outside the capture (lazy initialisation, allocator pools)
+            snap = [t.clone() for t in (state.flat, state.exp_avg, state.exp_avg_sq)]
+            self._body()
+            for t, c in zip((state.flat, state.exp_avg, state.exp_avg_sq), snap):
+                t.copy_(c)
+            self.step_dev.fill_(state.step)
+            self.n_overflow.zero_()
+        torch.cuda.current_stream(state.device).wait_stream(side)
+        self.graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(self.graph, capture_error_mode="relaxed"):
+            self._body()
+
+    def _body(self):
+        st, s = self.state, self.s
+        loss, _R, radii, g2d, _ = _C.refine_grad(
+            st.flat, st.grad, st.offsets(), st.P, s.bg, s.viewmatrices, s.projmatrices, s.campos, float(s.tanfovx),
+            float(s.tanfovy), float(s.kernel_size), float(s.scale_modifier), int(s.image_height), int(s.image_width),
+            int(s.sh_degree), self.gt, self.total_views, self.lambda_l1, bool(s.require_coord), bool(s.require_depth),
+            False, None, [], self.capacity, self.status)
+        self.loss.copy_(loss)
+        self.radii, self.g2d = radii, g2d
+        self.n_overflow.add_(self.status[1:2])
+        _C.adam_step_groups(st.flat, st.grad, st.exp_avg, st.exp_avg_sq, [st.P * k for _, k in GROUPS],
+                            [float(st.lrs[n]) for n, _ in GROUPS], 0.9, 0.999, 1e-15, 1, skip=self.status[1:2],
+                            step_dev=self.step_dev)
+
+    def run(self, viewmatrices, projmatrices, campos, gt) -> torch.Tensor:
+        """One iteration on the given cameras / targets (device tensors of the captured shapes); returns the loss
+        (a device scalar that the next run overwrites)."""
+        self.s.viewmatrices.copy_(viewmatrices)
+        self.s.projmatrices.copy_(projmatrices)
+        self.s.campos.copy_(campos)
+        self.gt.copy_(gt)
+        self.graph.replay()
+        self.replays += 1
+        return self.loss
+
+    def finish(self) -> int:
+        """Folds the device-side step count back into the state; returns the number of overflowed (skipped) iterations."""
+        self.state.step = int(self.step_dev.item())
+        return int(self.n_overflow.item())

@@ -38,7 +38,7 @@ class StreamConfig(NamedTuple):
     control_max: bool = True
     min_opacity: float = 0.005          # literal at infer_batch.py:320
     radius: float = 1.0                 # batch["radius"][0]: scene extent used by densify_and_prune
-    percent_dense: float = 0.01
+    percent_dense: float = 0.0          # GaussianModel.__init__ (gaussian_model.py:84); load_fromstream never changes it
     views_per_step: int = 1
     lrs: Optional[dict] = None          # training_lr; None -> refine.DEFAULT_LRS
 
@@ -105,7 +105,9 @@ def refine_keyframe(state: refine.RefineState, views: MultiViewSettings, gt: tor
         losses[it] = r.loss
         densified = False
         if cfg.use_densify and it < cfg.densify_until_iter:
-            stats.update(r.grad_means2D, r.radii)
+            if st.tile_rows is not None:
+                raise ValueError("densification statistics need whole views (tile-row bands would be counted twice)")
+            stats.update(r.grad_means2D, r.radii, grad_scale=float(len(step_views)))   # back on the per-view scale
             if it > cfg.densify_from_iter and it % cfg.densification_interval == 0:
                 stats.all_reduce(group)
                 densify_and_prune(state, stats, cfg.densify_grad_threshold, cfg.min_opacity, cfg.radius, None,

@@ -42,9 +42,9 @@
  *     The three forward buffers are opaque, self-describing (header + (P,V,R,W*H)) and must be handed
  *     back unchanged to igs_rasterize_backward (reference: ctx.save_for_backward,
  *     diff_gaussian_rasterization_rade/__init__.py:98-100).
- *   - All work is enqueued on `stream` (a cudaStream_t passed as void*).  The only host
- *     synchronisation in forward is one 8-byte D2H read of the instance count (the reference has the
- *     same one, rasterizer_impl.cu:354).
+ *   - All work is enqueued on `stream` (a cudaStream_t passed as void*).  In exact mode the only host
+ *     synchronisation in forward is one 4-byte D2H read of the instance count (the reference has the
+ *     same one, rasterizer_impl.cu:354); in capacity mode (igs_forward_args.instance_capacity) there is none.
  *   - Return value: 0 on success, negative igs_status otherwise.  igs_last_error() gives a message.
  *     There is NO CPU fallback: without a CUDA device every compute entry point returns
  *     IGS_ERR_CUDA.
@@ -59,7 +59,7 @@
 extern "C" {
 #endif
 
-#define IGS_RASTER_ABI_VERSION 5
+#define IGS_RASTER_ABI_VERSION 6
 
 typedef enum igs_status {
   IGS_OK = 0,
@@ -112,6 +112,16 @@ typedef struct igs_forward_args {
    * pixels.  Per-pixel results inside the window are identical to the full render.  Used to shard ONE view over
    * several GPUs (igs_b200.refine.shard_units); the reference has no equivalent. */
   const int* tile_rows;
+  /* Capacity mode (0 = exact mode, the reference's behaviour: one host read of the instance count R, reference
+   * rasterizer_impl.cu:354).  With instance_capacity > 0 the call makes NO host round-trip: the binning buffer is sized
+   * for `instance_capacity` instances, *num_rendered returns that capacity (hand it to igs_rasterize_backward as R), and
+   * every launch reads the true count on the device.  If the true count exceeds the capacity the surplus instances (the
+   * farthest Gaussians' tiles) are dropped and status[1] is set: the caller must discard the result and call again with
+   * a larger capacity (igs_adam_step_groups can be given the flag so that the parameter update becomes a no-op on the
+   * device).  status: optional DEVICE array of 2 words, written by every call: {true instance count, overflow flag}.
+   * A forward + backward in capacity mode can be captured in a CUDA graph. */
+  int instance_capacity;
+  unsigned int* status;
 } igs_forward_args;
 
 /* Forward.  *num_rendered receives R = total number of (Gaussian, tile) instances over all views
@@ -215,6 +225,13 @@ int igs_adam_step(float* param, const float* grad, float* exp_avg, float* exp_av
 int igs_adam_step_groups(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int ngroups,
                          const size_t* sizes, const float* lrs, float beta1, float beta2, float eps, int step,
                          void* stream);
+/* The same step guarded on the DEVICE: if skip_if_nonzero != NULL and *skip_if_nonzero != 0 when the kernel runs, nothing
+ * is updated (capacity mode of igs_rasterize_forward: pass &status[1]).  step_dev (optional DEVICE int): when given, the
+ * bias corrections use *step_dev + 1 and the kernel increments it if it updates — the step count then lives on the device
+ * and a skipped step is not counted, which is what a CUDA-graph replay of the iteration needs; `step` is ignored then. */
+int igs_adam_step_groups_guarded(float* param, const float* grad, float* exp_avg, float* exp_avg_sq, int ngroups,
+                                 const size_t* sizes, const float* lrs, float beta1, float beta2, float eps, int step,
+                                 const unsigned int* skip_if_nonzero, int* step_dev, void* stream);
 
 /* Fused refine loss over V images [V][3][H][W] (replaces infer_batch.py:301-305 with igs/utils/loss_utils.py:16-62):
  *   *loss_sum = sum_v [ lambda * mean|pred_v - gt_v| + (1 - lambda) * (1 - mean SSIM(pred_v, gt_v)) ]
@@ -257,9 +274,12 @@ int igs_activate_backward(int P, const float* scales, const float* raw_rot, cons
 /* Densification statistics of one step, all V views at once (igs/models/gaussian_model.py:865-868
  * `add_densification_stats` and the max_radii2D update of infer_batch.py:312-313, which the reference runs once per
  * single-view iteration):  for every view v with radii[v][g] > 0:  grad_accum[g] += |dL_dmeans2D[v][g].xy|,
- * denom[g] += 1, max_radii2D[g] = max(max_radii2D[g], radii[v][g]).  dL_dmeans2D is [V][P][3], radii [V][P]. */
-int igs_densify_stats(int P, int V, const float* dL_dmeans2D, const int* radii, float* grad_accum, float* denom,
-                      float* max_radii2D, void* stream);
+ * denom[g] += 1, max_radii2D[g] = max(max_radii2D[g], radii[v][g]).  dL_dmeans2D is [V][P][3], radii [V][P].
+ * grad_scale multiplies the norm: a step whose loss is the MEAN over its V views hands in gradients that are 1/V of the
+ * reference's per-view gradients (infer_batch.py:302-313 does not divide), so the caller passes V to keep
+ * densify_grad_threshold on the reference's scale. */
+int igs_densify_stats(int P, int V, const float* dL_dmeans2D, const int* radii, float grad_scale, float* grad_accum,
+                      float* denom, float* max_radii2D, void* stream);
 
 /* Re-layout of the packed parameter record and both Adam moments after densify / prune, in one pass (replaces the
  * torch.cat / boolean-index rebuild of every nn.Parameter and optimizer state in igs/models/gaussian_model.py:466-557,
@@ -275,6 +295,16 @@ int igs_densify_gather(int P_old, int P_new, const int* src, const unsigned char
                        float split_div, const size_t* off_old, const size_t* off_new, const float* param_old,
                        const float* exp_avg_old, const float* exp_avg_sq_old, float* param_new, float* exp_avg_new,
                        float* exp_avg_sq_new, void* stream);
+
+/* Instrumentation for bench.py's roofline (no reference equivalent): replays the forward traversal of a finished
+ * igs_rasterize_forward call without producing any image and ADDS to counts (DEVICE array of 4 u64):
+ *   [0] (8x4 pixel block, instance) pairs that passed the block-level cull and were evaluated per pixel ("hits")
+ *   [1] (pixel, instance) pairs whose exponent was evaluated on a pixel that was still open   (E': MUFU work)
+ *   [2] (pixel, instance) pairs that were blended                                             (C: contributing pairs)
+ *   [3] instances staged (tile-list entries visited by their tile's CTA)                                         */
+int igs_count_blend_pairs(int P, int V, int R, int width, int height, const char* geom_buffer,
+                          const char* binning_buffer, const char* image_buffer, unsigned long long* counts,
+                          void* stream);
 
 const char* igs_last_error(void);
 int igs_abi_version(void);

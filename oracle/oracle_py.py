@@ -39,6 +39,12 @@ def num_threads() -> int:
     return int(lib().oracle_num_threads())
 
 
+def set_num_threads(n: int) -> int:
+    """OpenMP threads for the following oracle calls (returns the count in effect; 1 without OpenMP)."""
+    lib().oracle_set_num_threads.restype = C.c_int
+    return int(lib().oracle_set_num_threads(C.c_int(int(n))))
+
+
 class _Geom(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("depths", "means2D", "conic_opacity", "rgb", "cov3D", "view_points",
                                           "camera_planes", "ray_planes", "ts", "normals", "clamped", "radii",

@@ -25,7 +25,8 @@ def test_header_declares_the_expected_entry_points():
     fns = declared_functions()
     for must in ("igs_rasterize_forward", "igs_rasterize_backward", "igs_mark_visible", "igs_decode_binning",
                  "igs_adam_step", "igs_adam_step_groups", "igs_refine_loss", "igs_activate_forward",
-                 "igs_activate_backward", "igs_last_error", "igs_abi_version", "igs_kernel_launches"):
+                 "igs_activate_backward", "igs_last_error", "igs_abi_version", "igs_kernel_launches",
+                 "igs_adam_step_groups_guarded", "igs_count_blend_pairs", "igs_densify_stats", "igs_densify_gather"):
         assert must in fns
 
 
@@ -35,7 +36,7 @@ def test_every_declared_symbol_is_exported(lib):
 
 
 def test_abi_version(lib):
-    assert lib.igs_abi_version() == 5
+    assert lib.igs_abi_version() == 6
 
 
 def test_null_arguments_are_rejected_without_touching_the_gpu(lib):

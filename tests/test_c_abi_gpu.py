@@ -23,7 +23,8 @@ class Fwd(C.Structure):
                 [(n, C.c_float) for n in ("tan_fovx", "tan_fovy", "kernel_size")] +
                 [(n, C.c_int) for n in ("prefiltered", "require_coord", "require_depth", "debug")] +
                 [(n, C.c_void_p) for n in ("out_color", "out_coord", "out_mcoord", "out_depth", "out_mdepth", "out_alpha",
-                                           "out_normal", "radii", "tile_rows")])
+                                           "out_normal", "radii", "tile_rows")] +
+                [("instance_capacity", C.c_int), ("status", C.c_void_p)])
 
 
 class Bwd(C.Structure):

@@ -11,7 +11,12 @@ rows = list(csv.reader(io.StringIO(out)))
 print(rows[0][1][:120])
 hdr = rows[1]
 iS, iI, iSm, iW, iT = (hdr.index(x) for x in ("Source", "Instructions Executed", "# Samples", "L1 Wavefronts Shared", "Avg. Threads Executed"))
-lines = [(int(r[iI]), int(r[iSm]), int(r[iW]), r[iS].strip(), r[iT]) for r in rows[2:] if len(r) > iW]
+body = rows[2:]
+for k, r in enumerate(body):   # several kernels in one report: keep the first (or the one selected with --kernel N)
+    if r and r[0] == "Kernel Name":
+        body = body[:k]
+        break
+lines = [(int(r[iI]), int(r[iSm]), int(r[iW]), r[iS].strip(), r[iT]) for r in body if len(r) > iW]
 tot = sum(l[0] for l in lines); ts = sum(l[1] for l in lines)
 print(f"total warp instructions {tot/1e9:.3f} G, samples {ts}, shared wavefronts {sum(l[2] for l in lines)/1e9:.3f} G")
 regs, cur = [], None
