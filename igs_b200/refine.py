@@ -61,6 +61,7 @@ class RefineState:
         self._pending = []            # (n_views, pinned host mirror of `status`, event) not yet looked at
         self.overflows = 0            # forwards whose capacity was exceeded (their Adam step was skipped on the device)
         self.status = torch.zeros(2, dtype=torch.int32, device=self.device)
+        self.last_guarded = False     # did the latest refine_iteration run its forward in capacity mode?
 
     # ---- capacity mode bookkeeping -------------------------------------------------------------------------------
     def enable_async_binning(self, on: bool = True, margin: float = 1.2) -> None:
@@ -115,6 +116,7 @@ class RefineState:
         self.P = P
         self.flat, self.exp_avg, self.exp_avg_sq = flat, exp_avg, exp_avg_sq
         self.grad = torch.zeros(n, device=self.device, dtype=torch.float32)
+        self._r_seen = {}             # instance counts of the old Gaussian set say nothing about the new one
         off = 0
         for name, k in GROUPS:
             self.slices[name] = (off, off + P * k, k)
@@ -252,6 +254,7 @@ def refine_iteration(state: RefineState, settings: MultiViewSettings, gt: torch.
         else:
             state.track_status(Vl)               # capacity mode: the count is looked at later, without a sync
         guarded = cap != 0
+        state.last_guarded = guarded
         if guarded and group is not None and torch.distributed.get_world_size(group) > 1:
             # one rank's overflow must skip the step on EVERY rank: fold the flag into the exchange
             torch.distributed.all_reduce(state.status[1:2], op=torch.distributed.ReduceOp.MAX, group=group)
@@ -259,6 +262,7 @@ def refine_iteration(state: RefineState, settings: MultiViewSettings, gt: torch.
         if do_step:
             state.adam_step(guarded=guarded)
         return IterationResult(loss, int(R), radii, g2d)
+    state.last_guarded = False
     names = [n for n, _ in GROUPS]
     leaves = []
     for n in names:

@@ -40,6 +40,10 @@ class StreamConfig(NamedTuple):
     radius: float = 1.0                 # batch["radius"][0]: scene extent used by densify_and_prune
     percent_dense: float = 0.0          # GaussianModel.__init__ (gaussian_model.py:84); load_fromstream never changes it
     views_per_step: int = 1
+    # "exact": every forward reads its instance count back (the reference's behaviour, rasterizer_impl.cu:354);
+    # "async": capacity mode after the key frame's first iteration, no host round-trip (refine.RefineState);
+    # "graph": as "async", and the whole iteration is ONE CUDA-graph replay (single rank, densify off)
+    mode: str = "exact"
     lrs: Optional[dict] = None          # training_lr; None -> refine.DEFAULT_LRS
 
 
@@ -73,6 +77,7 @@ class KeyframeResult(NamedTuple):
     schedule: List[List[int]]
     P: int                      # Gaussians after the loop (densify / prune change it)
     densified_at: List[int]
+    redone: int = 0             # capacity-mode iterations whose instance count overflowed and were run again
 
 
 def refine_keyframe(state: refine.RefineState, views: MultiViewSettings, gt: torch.Tensor, cfg: StreamConfig,
@@ -96,6 +101,14 @@ def refine_keyframe(state: refine.RefineState, views: MultiViewSettings, gt: tor
     sched = view_schedule(V, cfg.refine_iterations, rng, cfg.views_per_step)
     losses = torch.zeros(cfg.refine_iterations, device=state.device)
     densified_at = []
+    if cfg.mode not in ("exact", "async", "graph"):
+        raise ValueError(f"unknown stream mode {cfg.mode!r}")
+    if cfg.mode == "graph" and (world > 1 or cfg.use_densify):
+        raise ValueError('mode="graph" is single-rank and needs densify off (the Gaussian count must not change)')
+    state.enable_async_binning(cfg.mode == "async")
+    if cfg.mode == "graph":
+        return _refine_keyframe_graphed(state, views, gt, cfg, sched, losses)
+    overflows0 = state.overflows
     for it, step_views in enumerate(sched):
         mine = step_views[rank::world]
         st = select_views(views, mine)
@@ -117,8 +130,47 @@ def refine_keyframe(state: refine.RefineState, views: MultiViewSettings, gt: tor
         # The reference's densify_and_prune replaces every nn.Parameter, so the `optimizer.step()` that follows it in
         # the same iteration sees grad=None and updates nothing (infer_batch.py:320-324): no Adam step here either.
         if not densified:
-            state.adam_step()
-    return KeyframeResult(losses, sched, state.P, densified_at)
+            state.adam_step(guarded=state.last_guarded)
+    redone = 0
+    if state.async_binning:
+        # an iteration whose instance count exceeded its capacity skipped its own Adam step on the device; the count
+        # is known by now (one synchronisation per key frame), so the same number of iterations is run again
+        state.poll_status(wait=True)
+        redone = state.overflows - overflows0
+        for k in range(redone):
+            mine = sched[-1 - k % len(sched)][rank::world]
+            st = select_views(views, mine)
+            gt_step = gt[mine[0]:mine[0] + 1] if len(mine) == 1 else gt[torch.tensor(mine, device=gt.device)]
+            state.enable_async_binning(False)
+            refine.refine_iteration(state, st, gt_step, len(sched[-1]), group=group, lambda_l1=cfg.lambda_l1)
+            state.enable_async_binning(True)
+    return KeyframeResult(losses, sched, state.P, densified_at, redone)
+
+
+def _refine_keyframe_graphed(state, views, gt, cfg, sched, losses) -> KeyframeResult:
+    """The key frame's iterations as CUDA-graph replays: iteration 0 runs eagerly in exact mode (it tells the instance
+    count), the others replay ONE captured iteration with the step's cameras / targets copied into its static buffers."""
+    def inputs(step_views):
+        if len(step_views) == 1:
+            v = step_views[0]
+            return select_views(views, step_views), gt[v:v + 1]
+        return select_views(views, step_views), gt[torch.tensor(step_views, device=gt.device)]
+
+    st0, gt0 = inputs(sched[0])
+    r = refine.refine_iteration(state, st0, gt0, len(sched[0]), lambda_l1=cfg.lambda_l1)
+    losses[0] = r.loss
+    redone = 0
+    if len(sched) > 1:
+        cap = (int(r.num_rendered * 1.3) + 4095) // 4096 * 4096 + 4096
+        g = refine.GraphedIteration(state, st0, gt0, len(sched[0]), cap, cfg.lambda_l1)
+        for it in range(1, len(sched)):
+            st, gts = inputs(sched[it])
+            losses[it] = g.run(st.viewmatrices, st.projmatrices, st.campos, gts)
+        redone = g.finish()
+        for k in range(redone):   # overflowed replays skipped their step: run as many eager iterations
+            st, gts = inputs(sched[-1 - k % len(sched)])
+            refine.refine_iteration(state, st, gts, len(sched[-1]), lambda_l1=cfg.lambda_l1)
+    return KeyframeResult(losses, sched, state.P, [], redone)
 
 
 def render_view(state: refine.RefineState, views: MultiViewSettings, v: int) -> torch.Tensor:

@@ -94,3 +94,20 @@ def test_stream_improves_psnr_and_carries_gaussians(cuda_dev, native):
     assert len(res.psnrs) == 3 and res.iterations == 60 and res.points_num == [P] * 3
     assert res.psnrs[0] > before + 1.0 and res.psnrs[-1] >= res.psnrs[0] - 0.5
     assert all(t > 0 for t in res.keyframe_ms)
+
+
+@pytest.mark.parametrize("mode", ["async", "graph"])
+def test_keyframe_modes_without_host_round_trip_match_the_exact_loop(cuda_dev, native, mode):
+    """mode="async" (capacity mode) and mode="graph" (one CUDA-graph replay per iteration) run the same iterations as
+    the exact loop: same view draws, same losses, same parameters (the graph computes Adam's bias corrections on the
+    device, hence the last-bit tolerance)."""
+    from igs_b200 import stream
+    P, V, W, H, iters = 8000, 4, 160, 120, 8
+    _sc, _cams, st, a = _setup(cuda_dev, P, V, W, H)
+    _sc, _cams, _st, b = _setup(cuda_dev, P, V, W, H)
+    gt = torch.rand(V, 3, H, W, generator=torch.Generator().manual_seed(7)).to(cuda_dev)
+    ra = stream.refine_keyframe(a, st, gt, stream.StreamConfig(refine_iterations=iters), random.Random(5))
+    rb = stream.refine_keyframe(b, st, gt, stream.StreamConfig(refine_iterations=iters, mode=mode), random.Random(5))
+    assert ra.schedule == rb.schedule and rb.redone == 0 and a.step == b.step == iters
+    assert float((ra.losses - rb.losses).abs().max()) <= 1e-5 * float(ra.losses.abs().max())
+    assert float((a.flat - b.flat).abs().max()) <= 1e-5 * float(a.flat.abs().max())

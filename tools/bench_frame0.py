@@ -52,14 +52,22 @@ def main():
         for i in range(3):
             it(i)
         torch.cuda.synchronize()
+        sampler = clocks.ClockSampler(0, period_s=0.01)
+        sampler.start()
+        sampler.begin()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         for i in range(steps):
             out = it(i)
         e1.record()
         torch.cuda.synchronize()
+        sampler.end()
+        clock_records.append(clocks.verdict(sampler.stop()))
         return e0.elapsed_time(e1) / steps, float(out.loss), float(out.depth_normal_loss)
 
+    sys.path.insert(0, str(ROOT / "tools"))
+    import clocks
+    clock_records = []
     l0 = _C.kernel_launches()
     ours = run(None, "fused", args.steps)
     launches = (_C.kernel_launches() - l0) / (args.steps + 3)
@@ -72,7 +80,9 @@ def main():
         "ours_fused_ms": ours[0], "ours_rasterizer_with_torch_losses_ms": ours_torch_losses[0],
         "reference_cuda_ms": None if refr is None else refr[0], "igs_kernel_launches_per_iteration": launches,
         "loss": {"ours": ours[1], "ours_torch_losses": ours_torch_losses[1], "reference": None if refr is None else refr[1]},
-        "depth_normal_loss": {"ours": ours[2], "reference": None if refr is None else refr[2]}}), flush=True)
+        "depth_normal_loss": {"ours": ours[2], "reference": None if refr is None else refr[2]},
+        "clocks": {"ours_fused": clock_records[0], "ours_torch_losses": clock_records[1],
+                   "reference": clock_records[2] if len(clock_records) > 2 else None}}), flush=True)
 
 
 if __name__ == "__main__":

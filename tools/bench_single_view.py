@@ -56,6 +56,9 @@ def main():
         for _ in range(5):
             fwd_bwd()
         torch.cuda.synchronize()
+        sampler = clocks.ClockSampler(0, period_s=0.01)
+        sampler.start()
+        sampler.begin()
         e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
         e[0].record()
         for _ in range(steps):
@@ -66,9 +69,13 @@ def main():
                 fwd()
         e[2].record()
         torch.cuda.synchronize()
+        sampler.end()
         f = e[1].elapsed_time(e[2]) / steps
-        return {"fwd_bwd_ms": e[0].elapsed_time(e[1]) / steps, "fwd_ms": f, "fwd_mpix_s": W * H / 1e6 / (f / 1e3)}
+        return {"fwd_bwd_ms": e[0].elapsed_time(e[1]) / steps, "fwd_ms": f, "fwd_mpix_s": W * H / 1e6 / (f / 1e3),
+                "clocks": clocks.verdict(sampler.stop())}
 
+    sys.path.insert(0, str(ROOT / "tools"))
+    import clocks
     l0 = _C.kernel_launches()
     a = run(ours, args.steps)
     a["igs_kernel_launches_per_fwd_bwd_plus_fwd"] = (_C.kernel_launches() - l0) / (args.steps + 5 + args.steps)

@@ -31,6 +31,9 @@ def main():
     ap.add_argument("--densify", action="store_true")
     ap.add_argument("--no-ref", action="store_true")
     ap.add_argument("--ref-keyframes", type=int, default=2)
+    ap.add_argument("--mode", default="graph", choices=["exact", "async", "graph"],
+                    help="exact: host read of the instance count per forward (reference behaviour); async: capacity mode; "
+                         "graph: one CUDA-graph replay per iteration (default; falls back to async with --densify)")
     args = ap.parse_args()
 
     import torch
@@ -60,29 +63,37 @@ def main():
     def fresh_state():
         return refine.RefineState(sc.xyz + xyz_noise, sc.log_scale, sc.rot, sc.opacity_logit, sc.sh + sh_noise, dev)
 
+    mode = "async" if (args.densify and args.mode == "graph") else args.mode
     scfg = stream.StreamConfig(refine_iterations=args.iters, use_densify=args.densify, max_num=cfg["P"], radius=10.0,
-                               views_per_step=args.views_per_step)
+                               views_per_step=args.views_per_step, mode=mode)
+    sys.path.insert(0, str(ROOT / "tools"))
+    import clocks
     # warm-up: one short key frame (allocator, lazy module loads)
     stream.run_stream(fresh_state(), st, frames[:1], scfg._replace(refine_iterations=5), seed=1)
     state = fresh_state()
     torch.cuda.synchronize()
     l0 = _C.kernel_launches()
+    sampler = clocks.ClockSampler(0, period_s=0.02)
+    sampler.start()
+    sampler.begin()
     t0 = time.perf_counter()
     res = stream.run_stream(state, st, frames, scfg, seed=0)
     torch.cuda.synchronize()
     wall = time.perf_counter() - t0
+    sampler.end()
+    clk = clocks.verdict(sampler.stop())
     launches = _C.kernel_launches() - l0
     total_iters = args.iters * args.keyframes
     # where one iteration's time goes: the library's own stage timers over one more key frame (outside the timed run)
     _C.stage_timing_enable(True)
-    stream.run_stream(fresh_state(), st, frames[:1], scfg, seed=2)
+    stream.run_stream(fresh_state(), st, frames[:1], scfg._replace(mode="async" if mode == "graph" else mode), seed=2)
     torch.cuda.synchronize()
     stages = {n: round(ms / args.iters, 4) for n, ms, c in _C.stage_timing_read(True) if c > 0}
     _C.stage_timing_enable(False)
     ours = {"total_s": wall, "stage_ms_per_iteration": stages, "stage_ms_sum": round(sum(stages.values()), 4), "device_s": sum(res.keyframe_ms) / 1e3, "ms_per_iteration": wall * 1e3 / total_iters,
             "ms_per_keyframe": wall * 1e3 / args.keyframes, "psnr_first": res.psnrs[0], "psnr_last": res.psnrs[-1],
             "points_last": res.points_num[-1], "gpu_launches": int(launches),
-            "h2d_bytes_per_keyframe": int(frames[0].numel() * 4)}
+            "h2d_bytes_per_keyframe": int(frames[0].numel() * 4), "mode": mode, "clocks": clk}
 
     ref_line = None
     if not args.no_ref:

@@ -17,6 +17,21 @@ __global__ void __launch_bounds__(256) mufu_k(float* out, int iters) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = a;
 }
 
+// scalar FFMA: 16 independent chains per thread
+__global__ void __launch_bounds__(256) ffma_k(float* out, int iters) {
+  float x[16];
+#pragma unroll
+  for (int i = 0; i < 16; i++) x[i] = 0.001f * (threadIdx.x + i);
+  const float a = 1.0000001f, b = 1e-9f;
+  for (int it = 0; it < iters; it++) {
+#pragma unroll
+    for (int i = 0; i < 16; i++) asm volatile("fma.rn.f32 %0, %0, %1, %2;" : "+f"(x[i]) : "f"(a), "f"(b));
+  }
+  float s = 0;
+  for (int i = 0; i < 16; i++) s += x[i];
+  out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 __global__ void __launch_bounds__(256) lds_k(float* out, int iters) {
   __shared__ float4 buf[1024];
   for (int i = threadIdx.x; i < 1024; i += 256) buf[i] = make_float4(i, 1, 2, 3);
@@ -50,6 +65,10 @@ int main() {
   double winst = 148.0 * 8 * 8 * iters * 8;
   printf("{\"sm_clock_ghz_nominal\": %.3f,\n", ghz);
   printf(" \"mufu_ex2_warp_inst_per_clk_per_sm\": %.3f, \"mufu_ex2_ms\": %.3f,\n", winst / (t * 1e-3) / (ghz * 1e9) / 148, t);
+  t = timeit([&] { ffma_k<<<148 * 8, 256>>>(out, iters); });
+  winst = 148.0 * 8 * 8 * iters * 16;
+  printf(" \"ffma_warp_inst_per_clk_per_sm\": %.3f, \"ffma_tflops\": %.2f, \"ffma_ms\": %.3f,\n",
+         winst / (t * 1e-3) / (ghz * 1e9) / 148, winst * 64 / (t * 1e-3) / 1e12, t);
   t = timeit([&] { lds_k<<<148 * 8, 256>>>(out, iters); });
   winst = 148.0 * 8 * 8 * iters * 4;
   printf(" \"lds128_warp_inst_per_clk_per_sm\": %.3f, \"lds128_bytes_per_clk_per_sm\": %.1f, \"lds128_ms\": %.3f}\n",
