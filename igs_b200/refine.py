@@ -460,6 +460,11 @@ class GraphedIteration:
                             [float(st.lrs[n]) for n, _ in GROUPS], 0.9, 0.999, 1e-15, 1, skip=self.status[1:2],
                             step_dev=self.step_dev)
 
+    def begin(self, step: int) -> None:
+        """Start of a run of replays: the device-side Adam step count takes the state's, the overflow counter restarts."""
+        self.step_dev.fill_(int(step))
+        self.n_overflow.zero_()
+
     def run(self, viewmatrices, projmatrices, campos, gt) -> torch.Tensor:
         """One iteration on the given cameras / targets (device tensors of the captured shapes); returns the loss
         (a device scalar that the next run overwrites)."""

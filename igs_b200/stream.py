@@ -161,12 +161,24 @@ def _refine_keyframe_graphed(state, views, gt, cfg, sched, losses) -> KeyframeRe
     losses[0] = r.loss
     redone = 0
     if len(sched) > 1:
-        cap = (int(r.num_rendered * 1.3) + 4095) // 4096 * 4096 + 4096
-        g = refine.GraphedIteration(state, st0, gt0, len(sched[0]), cap, cfg.lambda_l1)
+        # Capturing costs far more than a key frame (torch.cuda.graph synchronises, collects garbage and empties the
+        # allocator cache), so the captured iteration is kept on the state and reused by later key frames as long as the
+        # shapes, the parameter storage and the capacity still fit.
+        key = (state.P, len(sched[0]), int(views.image_height), int(views.image_width), float(cfg.lambda_l1),
+               state.flat.data_ptr(), state.exp_avg.data_ptr(), tuple(sorted(state.lrs.items())))
+        g = getattr(state, "_graphed", None)
+        if g is None or g.key != key or g.capacity < int(r.num_rendered * 1.1):
+            cap = (int(r.num_rendered * 1.3) + 4095) // 4096 * 4096 + 4096
+            g = refine.GraphedIteration(state, st0, gt0, len(sched[0]), cap, cfg.lambda_l1)
+            g.key = key
+            state._graphed = g
+        g.begin(state.step)
         for it in range(1, len(sched)):
             st, gts = inputs(sched[it])
             losses[it] = g.run(st.viewmatrices, st.projmatrices, st.campos, gts)
         redone = g.finish()
+        if redone:
+            state._graphed = None   # the capacity was too small: capture again (with the new count) next time
         for k in range(redone):   # overflowed replays skipped their step: run as many eager iterations
             st, gts = inputs(sched[-1 - k % len(sched)])
             refine.refine_iteration(state, st, gts, len(sched[-1]), lambda_l1=cfg.lambda_l1)

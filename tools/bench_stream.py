@@ -31,9 +31,9 @@ def main():
     ap.add_argument("--densify", action="store_true")
     ap.add_argument("--no-ref", action="store_true")
     ap.add_argument("--ref-keyframes", type=int, default=2)
-    ap.add_argument("--mode", default="graph", choices=["exact", "async", "graph"],
+    ap.add_argument("--mode", default="async", choices=["exact", "async", "graph"],
                     help="exact: host read of the instance count per forward (reference behaviour); async: capacity mode; "
-                         "graph: one CUDA-graph replay per iteration (default; falls back to async with --densify)")
+                         "graph: one CUDA-graph replay per iteration (falls back to async with --densify)")
     args = ap.parse_args()
 
     import torch
