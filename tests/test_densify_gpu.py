@@ -86,3 +86,33 @@ def test_refine_loop_with_densification(cuda_dev, native):
     assert len(set(sizes)) > 1, sizes                      # the number of Gaussians did change
     assert all(math.isfinite(x) for x in losses) and losses[-1] < losses[0]
     assert bool(torch.isfinite(state.flat).all())
+
+
+@pytest.mark.parametrize("case", ["refine", "bounded", "cloned"])
+def test_kernels_match_the_reference_class(cuda_dev, native, case):
+    """igs_densify_stats + igs_densify_gather against what the reference's own GaussianModel produced
+    (tests/golden/ref_densify_*.npz, tools/make_golden_densify.py).  The split samples are planned on the CPU so that
+    the random stream is the reference's (global CPU generator)."""
+    import numpy as np
+    from igs_b200 import densify
+    from test_densify_host import GOLDEN, _check_against_golden, _state_from_golden
+    g = np.load(GOLDEN / f"ref_densify_{case}.npz")
+    P = int(g["cfg_P"])
+    stats = densify.DensifyStats(P, cuda_dev)
+    for i in range(3):
+        radii = torch.where(torch.from_numpy(g[f"stat{i}_vis"]), torch.from_numpy(g[f"stat{i}_radii"]), torch.zeros(P)).to(torch.int32)
+        stats.update(torch.from_numpy(g[f"stat{i}_grad"]).unsqueeze(0).to(cuda_dev), radii.unsqueeze(0).to(cuda_dev))
+    assert torch.allclose(stats.grad_accum.cpu(), torch.from_numpy(g["grad_accum"]).reshape(-1), rtol=1e-6, atol=0)
+    assert torch.equal(stats.denom.cpu(), torch.from_numpy(g["denom"]).reshape(-1))
+    assert torch.equal(stats.max_radii2D.cpu(), torch.from_numpy(g["max_radii2D"]).reshape(-1))
+    st_cpu = _state_from_golden(g)
+    plan = densify.plan_densify(None, st_cpu.param("scaling"), st_cpu.param("opacity"), torch.from_numpy(g["grad_accum"]).reshape(-1),
+                                torch.from_numpy(g["denom"]).reshape(-1), float(g["cfg_thr"]), 0.005, float(g["cfg_extent"]), None,
+                                int(g["cfg_max_num"]), float(g["cfg_percent_dense"]), True,
+                                generator=torch.Generator().manual_seed(int(g["cfg_rng_seed"])))
+    st = _state_from_golden(g, cuda_dev)
+    P_new = int(plan.src.numel())
+    flat, m, v = native.densify_gather(st.flat, st.exp_avg, st.exp_avg_sq, P, plan.src.to(cuda_dev), plan.kind.to(cuda_dev),
+                                       plan.samples.to(cuda_dev), float(plan.split_div), densify._offsets(P), densify._offsets(P_new))
+    st.resize(P_new, flat, m, v)
+    _check_against_golden(st, g)

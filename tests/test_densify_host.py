@@ -2,6 +2,9 @@
 GaussianModel.densify_and_prune (igs/models/gaussian_model.py:466-666) that rebuilds separate parameter tensors and
 Adam moments with torch.cat / boolean indexing like the reference does."""
 import math
+from pathlib import Path
+
+import numpy as np
 
 import pytest
 import torch
@@ -144,3 +147,70 @@ def test_stats_update_matches_reference_semantics():
         exp_acc[vis] += torch.norm(g2d[vv][vis, :2], dim=-1)
         exp_den[vis] += 1
     assert torch.equal(st.grad_accum, exp_acc) and torch.equal(st.denom, exp_den) and torch.equal(st.max_radii2D, exp_r)
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# Pin to the reference class itself: goldens written by tools/make_golden_densify.py, which runs the UNMODIFIED
+# /root/reference/igs/models/gaussian_model.py (fresh GaussianModel -> load_fromstream -> Adam steps -> statistics ->
+# densify_and_prune, the call path of infer_batch.py:266-324) in the build container.
+# ------------------------------------------------------------------------------------------------------------------
+GOLDEN = Path(__file__).resolve().parent / "golden"
+NAMES = ("xyz", "rotation", "shs", "opacity", "scaling")
+
+
+def _state_from_golden(g, device="cpu"):
+    t = {k: torch.from_numpy(g[f"pre_{k}"]) for k in NAMES}
+    st = refine.RefineState(t["xyz"], t["scaling"], t["rotation"], t["opacity"], t["shs"], device)
+    for k in NAMES:
+        st.view(st.exp_avg, k).copy_(torch.from_numpy(g[f"pre_m_{k}"]).reshape(st.view(st.exp_avg, k).shape))
+        st.view(st.exp_avg_sq, k).copy_(torch.from_numpy(g[f"pre_v_{k}"]).reshape(st.view(st.exp_avg_sq, k).shape))
+    return st
+
+
+def _check_against_golden(st, g, exact_moments=True):
+    P_new = g["post_xyz"].shape[0]
+    assert st.P == P_new
+    for k in NAMES:
+        got = st.param(k).detach().cpu().reshape(g[f"post_{k}"].shape)
+        ref = torch.from_numpy(g[f"post_{k}"])
+        if k in ("xyz", "scaling"):       # split children: R(q) * sample + xyz and log(exp(s) / 1.6), fp32 re-association
+            assert torch.allclose(got, ref, rtol=2e-6, atol=2e-6), k
+        else:
+            assert torch.equal(got, ref), k
+        for buf, tag in ((st.exp_avg, "m"), (st.exp_avg_sq, "v")):
+            got = st.view(buf, k).detach().cpu().reshape(g[f"post_{tag}_{k}"].shape)
+            assert torch.equal(got, torch.from_numpy(g[f"post_{tag}_{k}"])), (tag, k)
+
+
+@pytest.mark.parametrize("case", ["refine", "bounded", "cloned"])
+def test_statistics_and_densify_match_the_reference_class(case):
+    g = np.load(GOLDEN / f"ref_densify_{case}.npz")
+    P = int(g["cfg_P"])
+    # statistics: three single-view updates (add_densification_stats + the max_radii2D line of infer_batch.py:312)
+    stats = densify.DensifyStats(P, "cpu")
+    for i in range(3):
+        radii = torch.where(torch.from_numpy(g[f"stat{i}_vis"]), torch.from_numpy(g[f"stat{i}_radii"]), torch.zeros(P)).to(torch.int32)
+        stats.update_torch(torch.from_numpy(g[f"stat{i}_grad"]).unsqueeze(0), radii.unsqueeze(0))
+    assert torch.equal(stats.grad_accum, torch.from_numpy(g["grad_accum"]).reshape(-1))
+    assert torch.equal(stats.denom, torch.from_numpy(g["denom"]).reshape(-1))
+    assert torch.equal(stats.max_radii2D, torch.from_numpy(g["max_radii2D"]).reshape(-1))
+    # densify_and_prune with the reference's defaults for this path (percent_dense is whatever the golden's model had)
+    st = _state_from_golden(g)
+    gen = torch.Generator().manual_seed(int(g["cfg_rng_seed"]))   # the reference draws from the global CPU generator
+    plan = densify.plan_densify(None, st.param("scaling"), st.param("opacity"), stats.grad_accum, stats.denom,
+                                float(g["cfg_thr"]), 0.005, float(g["cfg_extent"]), None, int(g["cfg_max_num"]),
+                                float(g["cfg_percent_dense"]), True, generator=gen)
+    if case == "refine":
+        assert plan.n_clone == 0 and plan.n_split > 0      # percent_dense = 0: the refine loop never clones
+    if case == "cloned":
+        assert plan.n_clone > 0 and plan.n_split > 0
+    flat, m, v = densify.apply_plan_torch(st.flat, st.exp_avg, st.exp_avg_sq, P, plan)
+    st.resize(int(plan.src.numel()), flat, m, v)
+    _check_against_golden(st, g)
+
+
+def test_default_percent_dense_is_the_refine_paths_zero():
+    import inspect
+    from igs_b200 import stream
+    assert stream.StreamConfig().percent_dense == 0.0
+    assert inspect.signature(densify.densify_and_prune).parameters["percent_dense"].default == 0.0
