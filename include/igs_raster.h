@@ -258,6 +258,21 @@ int igs_depth_normal_loss(int use_coord, const float* map0, const float* map1, c
                           float* loss_sum, float* dL_dmap0, float* dL_dmap1, float* dL_dnormal, igs_alloc_fn temp_alloc,
                           void* temp_user, void* stream);
 
+/* igs_depth_normal_loss for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that
+ * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments,
+ * arithmetic and results as igs_depth_normal_loss, minus the allocator callback: the scratch (one double per 32x8-pixel
+ * tile for the deterministic loss reduction) lives in a file-scope __device__ array of IGS_NOALLOC_MAX_TILES doubles
+ * (512 KiB, held by every GPU that loads the library until the process exits), and the call makes no cudaMalloc /
+ * cudaFree / allocating library call.  Sizes with V * ceil(W/32) * ceil(H/8) > IGS_NOALLOC_MAX_TILES are rejected with
+ * IGS_ERR_UNSUPPORTED (e.g. 12 views of 1352x1014 or 2 views of 3840x2160 fit).  All calls on one device share the
+ * array: calls that overlap on the GPU (unordered streams) race on it and must be serialised by the caller.  The first
+ * call on a device resolves the array's address (cudaGetSymbolAddress) and should therefore happen outside a capture. */
+#define IGS_NOALLOC_MAX_TILES 65536
+int igs_depth_normal_loss_noalloc(int use_coord, const float* map0, const float* map1, const float* normal, int V,
+                                  int height, int width, float tan_fovx, float tan_fovy, float depth_ratio,
+                                  float grad_scale, float* loss_sum, float* dL_dmap0, float* dL_dmap1, float* dL_dnormal,
+                                  void* stream);
+
 /* Parameter activations of the refine loop and their chain rule (igs/models/gaussian_model.py:89-127, i.e.
  * RaDe-GS scene/gaussian_model.py setup_functions: scaling = exp, rotation = F.normalize (eps 1e-12),
  * opacity = sigmoid), one launch each instead of one torch kernel + autograd node per activation.
