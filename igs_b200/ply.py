@@ -26,9 +26,18 @@ def attribute_names(n_sh: int = 16, with_filter: bool = False):
     return names
 
 
-def save_ply(path, xyz, shs, opacity_logit, log_scale, rot, filter_3D: Optional[torch.Tensor] = None) -> None:
-    """xyz [P,3], shs [P,K,3], opacity_logit [P,1], log_scale [P,3], rot [P,4] (any device); values are written as
-    they are (pre-activation, like `save_ply(save_type='all')` after its inverse activations)."""
+def save_ply(path, xyz, shs, opacity_logit, log_scale, rot, filter_3D: Optional[torch.Tensor] = None,
+             normalize_rotation: bool = False) -> None:
+    """xyz [P,3], shs [P,K,3], opacity_logit [P,1], log_scale [P,3], rot [P,4] (any device), written pre-activation.
+
+    The reference has two writers for this layout.  The stream model's `save_ply` (igs/models/gs.py:317-342) writes
+    the stored fields as they are: that is the default here.  The refine model's `save_ply(save_type='all')`
+    (igs/models/gaussian_model.py:198-212) writes `get_rotation`, i.e. the NORMALISED quaternion (and opacity / scale
+    through inverse-activation(activation(.)), equal up to rounding): `normalize_rotation=True` gives that, so files
+    are value-compatible with reference-written ones for tools that assume unit quaternions.  Both are pinned by
+    tests/test_renderer_ref_host.py against files the reference's own code wrote."""
+    if normalize_rotation:
+        rot = torch.nn.functional.normalize(rot.detach().float())
     t = lambda a: a.detach().cpu().float().numpy()  # noqa: E731
     xyz, shs = t(xyz), t(shs)
     P, K = shs.shape[0], shs.shape[1]

@@ -49,6 +49,18 @@ def settings_from_c2ws(c2ws: torch.Tensor, FOV, resolution, bg: torch.Tensor, sh
                              0.0, bg, scale_modifier, wv, full.contiguous().float(), sh_degree, campos, True, True, False)
 
 
+def flow_colors(flow: Dict[str, torch.Tensor], viewmatrix: torch.Tensor, fx: float, fy: float) -> torch.Tensor:
+    """The per-Gaussian "colours" of the flow render (gs.py:693-700): the predicted displacement rotated into the camera
+    and scaled by focal / z — the reference divides by the WORLD z of the Gaussian, reproduced as is.  [Pm,3], third
+    channel zero."""
+    means3D = flow["xyz"]
+    flow_cam = flow["resi_xyz"] @ viewmatrix[:3, :3]
+    f2 = flow["resi_xyz"].new_zeros((means3D.shape[0], 3))
+    f2[:, 0] = flow_cam[:, 0] * fx / (means3D[:, 2] + 1e-6)
+    f2[:, 1] = flow_cam[:, 1] * fy / (means3D[:, 2] + 1e-6)
+    return f2
+
+
 def forward_single_batch(gs: Dict[str, torch.Tensor], c2ws: torch.Tensor, FOV, resolution, background_color: torch.Tensor,
                          sh_degree: int = 3, scaling_modifier: float = 1.0, flow: Optional[Dict[str, torch.Tensor]] = None,
                          flow_resolution=None, clamp: bool = True) -> Dict[str, torch.Tensor]:
@@ -85,10 +97,7 @@ def forward_single_batch(gs: Dict[str, torch.Tensor], c2ws: torch.Tensor, FOV, r
                                                campos=st.campos[v], prefiltered=False, require_depth=True, require_coord=True,
                                                debug=False)
             means3D = flow["xyz"]
-            flow_cam = flow["resi_xyz"] @ st.viewmatrices[v][:3, :3]
-            f2 = flow["resi_xyz"].new_zeros((means3D.shape[0], 3))
-            f2[:, 0] = flow_cam[:, 0] * fx / (means3D[:, 2] + 1e-6)    # the reference divides by WORLD z (gs.py:698-699)
-            f2[:, 1] = flow_cam[:, 1] * fy / (means3D[:, 2] + 1e-6)
+            f2 = flow_colors(flow, st.viewmatrices[v], fx, fy)
             r = GaussianRasterizerClamp(raster_settings=rs)(
                 means3D=means3D, means2D=torch.zeros_like(means3D, requires_grad=True), shs=None, colors_precomp=f2.float(),
                 opacities=flow["opacity"], scales=flow["scaling"], rotations=flow["rotation"], cov3D_precomp=None)
@@ -97,3 +106,44 @@ def forward_single_batch(gs: Dict[str, torch.Tensor], c2ws: torch.Tensor, FOV, r
         out["flow_pred"] = torch.stack(flows)
         out["flow_mask"] = torch.stack(masks)
     return out
+
+
+def quaternion_multiply(a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """Hamilton product of the NORMALISED quaternions (w, x, y, z) — igs/utils/general_utils.py:176-203."""
+    a, b = torch.nn.functional.normalize(a), torch.nn.functional.normalize(b)
+    w1, x1, y1, z1 = a.unbind(-1)
+    w2, x2, y2, z2 = b.unbind(-1)
+    return torch.stack([w1 * w2 - x1 * x2 - y1 * y2 - z1 * z2, w1 * x2 + x1 * w2 + y1 * z2 - z1 * y2,
+                        w1 * y2 + y1 * w2 + z1 * x2 - x1 * z2, w1 * z2 + z1 * w2 + x1 * y2 - y1 * x2], dim=-1)
+
+
+def deform(gs: Dict[str, torch.Tensor], resi: Dict[str, torch.Tensor], mask: torch.Tensor) -> Dict[str, torch.Tensor]:
+    """The streamed Gaussians moved by AGM-Net's predicted residuals (`GaussianModel.deform`, igs/models/gs.py:347-375):
+    gs = dict(xyz, opacity, rotation, scaling, shs) PRE-activation; on the masked Gaussians the rotation is composed
+    (quaternion product), `shs` [Pm,48] and every other residual are added.  Returns the deformed dict plus `mask` and
+    `resi_xyz` (what the flow render needs)."""
+    out = {k: gs[k].clone() for k in ("xyz", "opacity", "rotation", "scaling", "shs")}
+    for key, r in resi.items():
+        if key == "rotation":
+            out[key][mask] = quaternion_multiply(out[key][mask], r)
+        elif key == "shs":
+            out[key][mask] = r.reshape(-1, 16, 3) + out[key][mask]
+        else:
+            out[key][mask] = r + out[key][mask]
+    out["mask"] = mask
+    out["resi_xyz"] = resi["xyz"].clone()
+    return out
+
+
+def activated(gs: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """`get_xyz / get_features / get_opacity / get_scaling / get_rotation` of the stream model (gs.py:230-262)."""
+    return dict(xyz=gs["xyz"], shs=gs["shs"], opacity=torch.sigmoid(gs["opacity"]), scaling=torch.exp(gs["scaling"]),
+                rotation=torch.nn.functional.normalize(gs["rotation"]))
+
+
+def flow_inputs(deformed: Dict[str, torch.Tensor]) -> Dict[str, torch.Tensor]:
+    """The `flow` argument of forward_single_batch for a deformed model: the masked Gaussians AFTER the deformation
+    (the reference passes `original_gs = gs`, gs.py:846) and the predicted displacement (gs.py:686-695)."""
+    a, m = activated(deformed), deformed["mask"]
+    return dict(xyz=a["xyz"][m], opacity=a["opacity"][m], scaling=a["scaling"][m], rotation=a["rotation"][m],
+                resi_xyz=deformed["resi_xyz"])

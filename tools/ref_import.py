@@ -34,6 +34,13 @@ def _stub(name: str, **attrs):
     return m
 
 
+def _stub_plyfile():
+    """`plyfile` is absent from the image: tools/plyfile_min.py provides the few calls the reference makes."""
+    sys.path.insert(0, str(Path(__file__).resolve().parent))
+    import plyfile_min
+    _stub("plyfile", PlyData=plyfile_min.PlyData, PlyElement=plyfile_min.PlyElement)
+
+
 def load_file(dotted: str, rel: str):
     """Executes /root/reference/<rel> as module `dotted` (parents are stubbed as empty packages)."""
     parts = dotted.split(".")
@@ -53,14 +60,15 @@ def load_gaussian_model():
     """igs/models/gaussian_model.py (GaussianModel of the refine loop) with its helper modules loaded for real and
     the absent third-party / network-side imports stubbed."""
     _stub("icecream", ic=lambda *a, **k: None)
-    _stub("plyfile", PlyData=object, PlyElement=object)
+    _stub_plyfile()
     _stub("simple_knn")
     _stub("simple_knn._C", distCUDA2=None)
     load_file("igs.utils.general_utils", "igs/utils/general_utils.py")
     load_file("igs.utils.system_utils", "igs/utils/system_utils.py")
     load_file("igs.utils.graphics_utils", "igs/utils/graphics_utils.py")
     _stub("igs.models")
-    _stub("igs.models.gs", GaussianModel=object)   # only imported as a type name (gaussian_model.py:22)
+    if not hasattr(sys.modules.get("igs.models.gs"), "GS3DRenderer"):   # (keep the real module if load_gs_module ran)
+        _stub("igs.models.gs", GaussianModel=object)   # only imported as a type name (gaussian_model.py:22)
     return load_file("igs.models.gaussian_model", "igs/models/gaussian_model.py")
 
 
@@ -104,3 +112,71 @@ def cuda_as_cpu():
 class AttrDict(dict):
     """Stands in for the OmegaConf node `refine_item` (attribute and item access, `.keys()`)."""
     __getattr__ = dict.__getitem__
+
+
+class _Subscriptable:
+    """Stands in for jaxtyping's Float[Tensor, "..."] etc. in annotations."""
+    def __class_getitem__(cls, item):
+        return cls
+
+
+class RecordingRasterizer:
+    """Fake `diff_gaussian_rasterization_rade_clamp`: records what the reference renderer hands to the rasterizer
+    (settings + tensors) and returns blank maps of the right shapes, so the renderer-side code runs without a GPU."""
+    calls = []
+
+    class Settings(dict):
+        def __getattr__(self, k):
+            return self[k]
+
+    @staticmethod
+    def GaussianRasterizationSettings(**kw):
+        return RecordingRasterizer.Settings(kw)
+
+    class GaussianRasterizer:
+        def __init__(self, raster_settings):
+            self.s = raster_settings
+
+        def __call__(self, **kw):
+            RecordingRasterizer.calls.append((self.s, kw))
+            H, W, P = self.s["image_height"], self.s["image_width"], kw["means3D"].shape[0]
+            z = lambda c: torch.zeros(c, H, W)  # noqa: E731
+            return z(3), torch.zeros(P, dtype=torch.int32), z(3), z(3), z(1), z(1), z(1), z(3)
+
+
+def load_gs_module():
+    """igs/models/gs.py (Camera, stream GaussianModel, GS3DRenderer, load_ply / save_ply) with the network-side and
+    third-party imports stubbed and the clamp rasterizer replaced by `RecordingRasterizer`."""
+    import dataclasses
+    import typing
+    _stub("icecream", ic=lambda *a, **k: None)
+    _stub("fpsample")
+    _stub("open3d")
+    _stub("torch_cluster", fps=None, knn=None)
+    _stub_plyfile()
+    _stub("igs.models")
+    _stub("igs.models.networks", MLP=object)
+    ty = _stub("igs.utils.typing")
+    for n in ("Any", "Callable", "Dict", "Iterable", "List", "Literal", "NamedTuple", "NewType", "Optional", "Sized", "Tuple",
+              "Type", "TypeVar", "Union"):
+        setattr(ty, n, getattr(typing, n))
+    for n in ("Bool", "Complex", "Float", "Inexact", "Int", "Integer", "Num", "Shaped", "UInt"):
+        setattr(ty, n, _Subscriptable)
+    ty.Tensor = torch.Tensor
+    ty.DictConfig = dict
+    ty.__all__ = [n for n in vars(ty) if not n.startswith("_")]
+
+    class BaseModule(torch.nn.Module):
+        @dataclasses.dataclass
+        class Config:
+            pass
+    _stub("igs.utils.base", BaseModule=BaseModule)
+    _stub("igs.utils.ops", scale_tensor_batch=None, scale_tensor=None, select_points_bbox=None, position_embedding=None)
+    load_file("igs.utils.general_utils", "igs/utils/general_utils.py")
+    load_file("igs.utils.system_utils", "igs/utils/system_utils.py")
+    load_file("igs.utils.graphics_utils", "igs/utils/graphics_utils.py")
+    load_file("igs.utils.sh_utils", "igs/utils/sh_utils.py")
+    _stub("diff_gaussian_rasterization_rade_clamp",
+          GaussianRasterizationSettings=RecordingRasterizer.GaussianRasterizationSettings,
+          GaussianRasterizer=RecordingRasterizer.GaussianRasterizer)
+    return load_file("igs.models.gs", "igs/models/gs.py")
