@@ -1,5 +1,5 @@
 """GPU: the key-frame streaming refine loop (igs_b200/stream.py) against the loop a reference user writes
-(infer_batch.py:279-324: drop-in rasterizer module + torch loss + torch.optim.Adam), and end to end."""
+(infer_batch.py:279-324: the reference rasterizer build, baseline/_ref, + torch loss + torch.optim.Adam), and end to end."""
 import random
 
 import pytest
@@ -25,7 +25,11 @@ def test_keyframe_loop_matches_reference_users_loop(cuda_dev, native):
     """Same draws, same loss, same Adam: after 6 single-view iterations the parameters of the native loop and of the
     reference-style loop (drop-in module through autograd, refine_loss_torch, torch Adam eps=1e-15) agree."""
     import diff_gaussian_rasterization_rade as dgr
+    import ref_loader
     from igs_b200 import refine, stream
+    # the loop a reference user runs, on the REFERENCE rasterizer build when it travelled to the box (baseline/_ref);
+    # this repo's drop-in module only stands in where it did not
+    dgr = ref_loader.load_reference() or dgr
     P, V, W, H, iters = 8000, 4, 160, 120, 6
     sc, cams, st, state = _setup(cuda_dev, P, V, W, H)
     gt = torch.rand(V, 3, H, W, generator=torch.Generator().manual_seed(7)).to(cuda_dev)
