@@ -149,6 +149,7 @@ int igs_refine_loss(const float* pred, const float* gt, int V, int height, int w
                     void* stream) {
   if (V < 0 || height <= 0 || width <= 0 || !temp_alloc) { set_error("bad argument"); return IGS_ERR_INVALID; }
   if (loss_rows && V > 64) { set_error("loss_rows supports at most 64 views per call"); return IGS_ERR_UNSUPPORTED; }
+  if ((unsigned long long)height * (unsigned long long)width >= (1ull << 32)) { set_error("H*W exceeds the 32-bit in-plane offset range"); return IGS_ERR_UNSUPPORTED; }
   if (V == 0) return IGS_OK;
   if (!pred || !gt || !loss_sum || !dL_dpred) { set_error("null pointer"); return IGS_ERR_INVALID; }
   size_t bytes = refine_loss_scratch_bytes(V, height, width);

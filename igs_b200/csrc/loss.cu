@@ -13,6 +13,7 @@
 #include "common.cuh"
 #include "blend_common.cuh"
 #include "kernels.cuh"
+#include <cstdlib>
 
 namespace igs {
 
@@ -225,6 +226,7 @@ loss_pass1_kernel(LossParams p) {
       }
     }
     const int gx = x0 + c;
+    float accf = 0.0f;
     float* __restrict__ o_mu = p.dmu1 + po;
     float* __restrict__ o_11 = p.dE11 + po;
     float* __restrict__ o_12 = p.dE12 + po;
@@ -241,15 +243,16 @@ loss_pass1_kernel(LossParams p) {
       const float A = 2.0f * mu12 + C1, B = 2.0f * s12 + C2, Cc = mu1_sq + mu2_sq + C1, D = s1 + s2 + C2;
       const float inv = 1.0f / (Cc * D);
       const float ssim = A * B * inv;
-      // partials of ssim w.r.t. mu1 (E's held fixed), E11, E12
-      const float dmu1 = (2.0f * mu2 * B - 2.0f * mu2 * A) * inv - ssim * (2.0f * mu1 * D - 2.0f * mu1 * Cc) * inv;
-      const float d11 = -ssim / D;
+      // partials of ssim w.r.t. mu1 (E's held fixed), E11, E12;  1 / D = Cc * inv (one division per pixel)
+      const float dmu1 = 2.0f * inv * (mu2 * (B - A) - ssim * mu1 * (D - Cc));
+      const float d11 = -ssim * Cc * inv;
       const float d12 = 2.0f * A * inv;
       const uint32_t o = (uint32_t)gy * (uint32_t)p.W + (uint32_t)gx;
       o_mu[o] = dmu1; o_11[o] = d11; o_12[o] = d12;
       const float2 xy = sxy[rg * 4 + j + LOSS_R][c + LOSS_X0];
-      acc += (double)(p.lambda * fabsf(xy.x - xy.y)) - (double)((1.0f - p.lambda) * ssim);
+      accf += p.lambda * fabsf(xy.x - xy.y) - (1.0f - p.lambda) * ssim;   // four pixels in fp32, then double
     }
+    acc = (double)accf;
   }
   // block reduce (fixed order)
 #pragma unroll
@@ -369,9 +372,19 @@ loss_final_kernel(const double* __restrict__ partial, size_t n, double inv_n, do
   }
 }
 
+// Scratch: the three per-pixel partials (36 B / pixel) of all V views + one double per CTA.  ncu measured 3.57 GB of DRAM
+// traffic per step for this two-launch order (0.94 GB of partials written, 1.65 GB re-read) against 0.99 GB of algorithmic
+// bytes.  EXPERIMENT (IGS_LOSS_BY_VIEW=1): the two passes view by view over a single-view scratch (49 MB at 1352x1014), so
+// that the partials never leave the 126 MB L2 — measured SLOWER (2.16 vs 1.86 ms at C3): the kernels are issue / latency
+// bound, not DRAM bound, and 40 launches of 3.5 waves each lose more in their tails than the L2 hits win.  Off by default.
+static bool loss_by_view() {
+  static const bool on = [] { const char* e = getenv("IGS_LOSS_BY_VIEW"); return e && atoi(e) != 0; }();
+  return on;
+}
+
 size_t refine_loss_scratch_bytes(int V, int H, int W) {
-  size_t planes = (size_t)V * 3, N = (size_t)H * W;
-  size_t nblk = planes * ((W + LOSS_BX - 1) / LOSS_BX) * ((H + LOSS_BY - 1) / LOSS_BY);
+  size_t planes = (size_t)(loss_by_view() ? 1 : V) * 3, N = (size_t)H * W;
+  size_t nblk = (size_t)V * 3 * ((W + LOSS_BX - 1) / LOSS_BX) * ((H + LOSS_BY - 1) / LOSS_BY);
   return 3 * planes * N * sizeof(float) + 256 + nblk * sizeof(double) + 256;
 }
 
@@ -397,33 +410,56 @@ void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W,
     for (int x = 0; x < 11; x++) fsum += gf[x];  // torch: float32 tensor divided by its float32 sum
     for (int x = 0; x < 11; x++) p.win[x] = gf[x] / fsum;
   }
+  const bool by_view = loss_by_view();
   p.planes = V * 3; p.H = H; p.W = W; p.plane_per_view = 3; p.lambda = lambda;
   p.inv_n = grad_scale / (3.0f * (float)H * (float)W);  // only dL_dpred uses it; the loss value is finished in double
   p.pred = pred; p.gt = gt; p.dpred = dpred;
-  size_t N = (size_t)H * W, planes = (size_t)V * 3;
+  const size_t N = (size_t)H * W, planes = (size_t)(by_view ? 1 : V) * 3;
   p.dmu1 = reinterpret_cast<float*>(scratch);
   p.dE11 = p.dmu1 + planes * N;
   p.dE12 = p.dE11 + planes * N;
   size_t off = (3 * planes * N * sizeof(float) + 255) & ~size_t(255);
   p.partial = reinterpret_cast<double*>(scratch + off);
-  dim3 grid((W + LOSS_BX - 1) / LOSS_BX, (H + LOSS_BY - 1) / LOSS_BY, V * 3);
-  if (p.has_rows) {  // rows nobody here owns: zero partials (pass 2 reads a 5-row halo of them) and zero dL/dpred
-    cudaMemsetAsync(p.dmu1, 0, 3 * planes * N * sizeof(float), s);
-    cudaMemsetAsync(dpred, 0, planes * N * sizeof(float), s);
-  }
-  count_launch(3);
+  if ((size_t)H * W >= (1ull << 32)) return;  // in-plane offsets are 32-bit (igs_refine_loss rejects such sizes)
   // 16-byte staging loads need W % 4 == 0 (every float4 entirely inside or outside the image) and aligned planes
   const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(gt) |
                                      reinterpret_cast<uintptr_t>(p.dmu1)) % 16 == 0) && ((size_t)H * W < (1ull << 31));
-  if ((size_t)H * W >= (1ull << 32)) return;  // in-plane offsets are 32-bit (api.cu rejects such sizes earlier)
-  if (vec) {
-    loss_pass1_kernel<true><<<grid, 256, 0, s>>>(p);
-    loss_pass2_kernel<true><<<grid, 256, 0, s>>>(p);
+  const dim3 grid_all((W + LOSS_BX - 1) / LOSS_BX, (H + LOSS_BY - 1) / LOSS_BY, V * 3);
+  const size_t nblk = (size_t)grid_all.x * grid_all.y * grid_all.z;
+  if (p.has_rows) cudaMemsetAsync(dpred, 0, (size_t)V * 3 * N * sizeof(float), s);   // rows nobody here owns
+  if (!by_view) {
+    if (p.has_rows) cudaMemsetAsync(p.dmu1, 0, 3 * planes * N * sizeof(float), s);    // (pass 2 reads a 5-row halo of them)
+    count_launch(2);
+    if (vec) {
+      loss_pass1_kernel<true><<<grid_all, 256, 0, s>>>(p);
+      loss_pass2_kernel<true><<<grid_all, 256, 0, s>>>(p);
+    } else {
+      loss_pass1_kernel<false><<<grid_all, 256, 0, s>>>(p);
+      loss_pass2_kernel<false><<<grid_all, 256, 0, s>>>(p);
+    }
   } else {
-    loss_pass1_kernel<false><<<grid, 256, 0, s>>>(p);
-    loss_pass2_kernel<false><<<grid, 256, 0, s>>>(p);
+    const dim3 grid(grid_all.x, grid_all.y, 3);
+    const size_t nblk_view = (size_t)grid.x * grid.y * 3;
+    for (int v = 0; v < V; v++) {
+      LossParams q = p;
+      q.planes = 3;
+      q.pred = pred + (size_t)v * 3 * N; q.gt = gt + (size_t)v * 3 * N; q.dpred = dpred + (size_t)v * 3 * N;
+      q.partial = p.partial + (size_t)v * nblk_view;
+      if (p.has_rows) {
+        q.rows[0] = p.rows[2 * v]; q.rows[1] = p.rows[2 * v + 1];
+        cudaMemsetAsync(q.dmu1, 0, 9 * N * sizeof(float), s);   // the previous view's partials, outside this view's rows
+      }
+      count_launch(2);
+      if (vec) {
+        loss_pass1_kernel<true><<<grid, 256, 0, s>>>(q);
+        loss_pass2_kernel<true><<<grid, 256, 0, s>>>(q);
+      } else {
+        loss_pass1_kernel<false><<<grid, 256, 0, s>>>(q);
+        loss_pass2_kernel<false><<<grid, 256, 0, s>>>(q);
+      }
+    }
   }
-  size_t nblk = (size_t)grid.x * grid.y * grid.z;
+  count_launch(1);
   // sum_v (1 - lambda) * mean(1 - ssim) = (1 - lambda) * (owned rows / H) - (1 - lambda) * sum(ssim) / (3 H W)
   loss_final_kernel<<<1, 256, 0, s>>>(p.partial, nblk, 1.0 / (3.0 * (double)H * (double)W), owned_rows / (double)H * (1.0 - (double)lambda),
                                       loss_sum);
