@@ -55,6 +55,10 @@ def parse():
     ap.add_argument("--cpu-sample-views", type=int, default=2)
     ap.add_argument("--no-bands", dest="bands", action="store_false",
                     help="shard whole views only (v mod N) even when N does not divide the number of views")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="N > 1: fused = one kernel per rank over NVLS multicast (reduce-scatter + Adam on the slice + "
+                         "broadcast, csrc/exchange.cu; falls back to nccl where multicast is unavailable); nccl = "
+                         "ncclAllReduce + replicated Adam")
     ap.add_argument("--exact-binning", action="store_true",
                     help="read the instance count back on the host in every forward (reference behaviour) instead of the "
                          "capacity mode (igs_forward_args.instance_capacity)")
@@ -261,6 +265,10 @@ def main():
     # Stationary workload: against random targets Adam quickly drives opacities down, so the cost of a step would
     # depend on how many steps ran before it.  Every step therefore starts from the same parameters (one 70.8 MB
     # device-to-device copy inside the timed region); all of the step's work, Adam included, still runs.
+    exchange = "none"
+    if world > 1:
+        exchange = "fused (NVLS multicast kernel)" if (args.exchange == "fused" and state.enable_fused_exchange(group)) else \
+                   "nccl all-reduce + replicated Adam"
     snapshot = state.flat.clone()
     state.enable_async_binning(not args.exact_binning)   # the first step per view count runs exact and sizes the rest
 
@@ -435,8 +443,12 @@ def main():
     # ---- (2b) the exchange step alone (packed-gradient all-reduce), for the scaling analysis ----
     allreduce_ms = None
     if world > 1:
+        zero = torch.zeros((), device=dev)
+
         def only_reduce():
-            return refine.reduce_gradients(state.grad, torch.zeros((), device=dev), group)
+            if state.fused is not None:
+                return state.fused_exchange_step(zero, False)    # reduce + Adam + broadcast in one kernel (+ 2 barriers)
+            return refine.reduce_gradients(state.grad, zero, group)
         allreduce_ms, _ = timed(only_reduce, 10, 3)
 
     # ---- (3) end to end: host buffers in, loss out ----
@@ -572,7 +584,8 @@ def main():
         "clocks": clocks, "roofline": roofline, "cpu_baseline": cpu_baseline,
         "value_without_unused_geometry_maps": ms_lean, "fwd_mpix_s": fwd_mpix, "fwd_ms": ms_fwd, "loss": loss_val, "loss_impl": loss_impl,
         "num_rendered_rank0": int(R_true_local), "binning_capacity_rank0": int(R_local), "allreduce_ms": allreduce_ms,
-        "allreduce_bytes": int(state.grad.numel() * 4), "per_rank": per_rank, "view_assignment": assignment, "step_ms": step_stats.get("resident"), "first_attempt": first_attempt, "work": work, "stages": stage_report, "ref_cuda": ref_cuda,
+        "allreduce_bytes": int(state.grad.numel() * 4), "exchange": exchange,
+        "allreduce_ms_note": "fused: the whole exchange step (reduce + Adam + broadcast + 2 cross-rank barriers); nccl: the all-reduce alone", "per_rank": per_rank, "view_assignment": assignment, "step_ms": step_stats.get("resident"), "first_attempt": first_attempt, "work": work, "stages": stage_report, "ref_cuda": ref_cuda,
     }
     print(json.dumps(line), flush=True)
     if world > 1:

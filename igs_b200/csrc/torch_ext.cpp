@@ -555,6 +555,30 @@ std::tuple<torch::Tensor, int64_t, torch::Tensor, torch::Tensor, torch::Tensor> 
   return std::make_tuple(loss, (int64_t)rendered, std::get<8>(f), std::get<0>(b), status);
 }
 
+// Fused exchange (igs_fused_reduce_adam): grad_mc / param_mc are MULTICAST addresses (integers from the symmetric-memory
+// handle), everything else ordinary tensors of this rank.  Returns nothing; loss_out [1] float and skipped_out [1] int32
+// are written on the device.
+void FusedReduceAdam(int64_t grad_mc, int64_t param_mc, const torch::Tensor& param, torch::Tensor& exp_avg,
+                     torch::Tensor& exp_avg_sq, int64_t n, int64_t begin, int64_t end, const std::vector<int64_t>& sizes,
+                     const std::vector<double>& lrs, double beta1, double beta2, double eps, int64_t step,
+                     torch::Tensor& loss_out, torch::Tensor& skipped_out) {
+  TORCH_CHECK(param.is_cuda() && exp_avg.is_cuda() && exp_avg_sq.is_cuda() && loss_out.is_cuda() && skipped_out.is_cuda(),
+              "fused_reduce_adam needs CUDA tensors (there is no CPU path)");
+  TORCH_CHECK(grad_mc != 0 && param_mc != 0, "multicast addresses are null (no NVLS multicast support on this system?)");
+  TORCH_CHECK(param.numel() >= n && exp_avg.numel() >= n && exp_avg_sq.numel() >= n, "buffers shorter than n");
+  TORCH_CHECK(loss_out.scalar_type() == torch::kFloat32 && skipped_out.scalar_type() == torch::kInt32, "loss_out float32, skipped_out int32");
+  TORCH_CHECK(sizes.size() == lrs.size() && !sizes.empty() && sizes.size() <= 8, "1..8 groups");
+  std::vector<size_t> sz(sizes.begin(), sizes.end());
+  std::vector<float> lr(lrs.begin(), lrs.end());
+  const c10::cuda::CUDAGuard guard(param.device());
+  check(igs_fused_reduce_adam(reinterpret_cast<const float*>(grad_mc), reinterpret_cast<float*>(param_mc), param.data_ptr<float>(),
+                              exp_avg.data_ptr<float>(), exp_avg_sq.data_ptr<float>(), (size_t)n, (size_t)begin, (size_t)end,
+                              (int)sz.size(), sz.data(), lr.data(), (float)beta1, (float)beta2, (float)eps, (int)step,
+                              loss_out.data_ptr<float>(), reinterpret_cast<unsigned int*>(skipped_out.data_ptr<int>()),
+                              (void*)at::cuda::getCurrentCUDAStream().stream()),
+        "fused_reduce_adam");
+}
+
 void DensifyStats(const torch::Tensor& g2d, const torch::Tensor& radii, torch::Tensor& grad_accum, torch::Tensor& denom,
                   torch::Tensor& max_radii, double grad_scale) {
   TORCH_CHECK(g2d.is_cuda() && radii.is_cuda() && grad_accum.is_cuda(), "densify_stats needs CUDA tensors (there is no CPU path)");
@@ -621,6 +645,7 @@ PYBIND11_MODULE(TORCH_EXTENSION_NAME, m) {
         pybind11::arg("eps"), pybind11::arg("step"), pybind11::arg("skip") = pybind11::none(),
         pybind11::arg("step_dev") = pybind11::none());
   m.def("count_blend_pairs", &CountBlendPairs);
+  m.def("fused_reduce_adam", &FusedReduceAdam);
   m.def("densify_stats", &DensifyStats, pybind11::arg("dL_dmeans2D"), pybind11::arg("radii"), pybind11::arg("grad_accum"),
         pybind11::arg("denom"), pybind11::arg("max_radii2D"), pybind11::arg("grad_scale") = 1.0);
   m.def("densify_gather", &DensifyGather);

@@ -62,6 +62,76 @@ class RefineState:
         self.overflows = 0            # forwards whose capacity was exceeded (their Adam step was skipped on the device)
         self.status = torch.zeros(2, dtype=torch.int32, device=self.device)
         self.last_guarded = False     # did the latest refine_iteration run its forward in capacity mode?
+        self.fused = None             # symmetric buffers + handles of the fused exchange (enable_fused_exchange)
+
+    # ---- fused exchange over NVLink / NVSwitch multicast ------------------------------------------------------------
+    def enable_fused_exchange(self, group) -> bool:
+        """Moves the parameter and gradient records into SYMMETRIC memory bound to a multicast object
+        (torch.distributed._symmetric_memory: plumbing) so that the exchange step of a view-sharded iteration is ONE
+        kernel per rank — reduce-scatter of the gradients in the switch, Adam on the rank's 1/N slice, broadcast of the
+        updated slice (csrc/exchange.cu, igs_fused_reduce_adam) — instead of ncclAllReduce + a replicated Adam launch
+        (+ two 4-byte all-reduces for the loss and the overflow flag).  Returns False, leaving everything as it was,
+        where multicast is not available (then `reduce_gradients` + `adam_step` stay in use).  Collective: every rank
+        of `group` must call it."""
+        import torch.distributed as dist
+        self.fused = None
+        world = dist.get_world_size(group) if group is not None else 1
+        if world <= 1:
+            return False
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            n = self.P * FLOATS_PER_GAUSSIAN
+            n_pad = (n + 3) // 4 * 4
+            flat = symm_mem.empty(n_pad, dtype=torch.float32, device=self.device)
+            grad = symm_mem.empty(n_pad + 4, dtype=torch.float32, device=self.device)   # + tail slot {loss, overflow, 0, 0}
+            h_flat = symm_mem.rendezvous(flat, group)
+            h_grad = symm_mem.rendezvous(grad, group)
+            ok = int(h_flat.multicast_ptr) != 0 and int(h_grad.multicast_ptr) != 0   # 0: no NVLS multicast on this system
+        except Exception as ex:   # no symmetric memory / multicast on this system: keep the NCCL path
+            self.fused_error = f"{type(ex).__name__}: {ex}"
+            ok = False
+        flag = torch.tensor([1.0 if ok else 0.0], device=self.device)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+        if float(flag.item()) == 0.0:
+            return False
+        flat.zero_(); grad.zero_()
+        flat[:n].copy_(self.flat)
+        grad[:n].copy_(self.grad)
+        self.flat, self.grad = flat[:n], grad[:n]
+        def pad(t):
+            o = torch.zeros(n_pad, device=self.device)
+            o[:n].copy_(t)
+            return o
+        self._m_pad, self._v_pad = pad(self.exp_avg), pad(self.exp_avg_sq)
+        self.exp_avg, self.exp_avg_sq = self._m_pad[:n], self._v_pad[:n]
+        rank = dist.get_rank(group)
+        chunk = ((n_pad // 4) + world - 1) // world * 4
+        self.fused = dict(group=group, flat=flat, grad=grad, h_flat=h_flat, h_grad=h_grad, n=n, n_pad=n_pad,
+                          begin=min(n_pad, rank * chunk), end=min(n_pad, (rank + 1) * chunk),
+                          loss=torch.zeros(1, device=self.device), skipped=torch.zeros(1, dtype=torch.int32, device=self.device))
+        h_grad.barrier(channel=0)
+        return True
+
+    def fused_exchange_step(self, partial_loss: torch.Tensor, guarded: bool) -> torch.Tensor:
+        """gradients of all ranks -> Adam on this rank's slice -> parameters of all ranks, one kernel (see
+        enable_fused_exchange).  Returns the step's loss (sum of the ranks' partial losses), a device scalar."""
+        f = self.fused
+        n, n_pad = f["n"], f["n_pad"]
+        tail = f["grad"][n_pad:n_pad + 2]
+        tail[0:1].copy_(partial_loss.reshape(1))
+        if guarded:
+            tail[1:2].copy_(self.status[1:2])          # int32 0 / 1 -> float
+        else:
+            tail[1:2].zero_()
+        self.step += 1
+        sizes = [self.P * k for _, k in GROUPS]
+        sizes[-1] += n_pad - n                           # the pad floats ride in the last group (zero gradient: no-op)
+        f["h_grad"].barrier(channel=0)                   # every rank's gradients and tail slot are complete
+        _C.fused_reduce_adam(int(f["h_grad"].multicast_ptr), int(f["h_flat"].multicast_ptr), f["flat"], self._m_pad, self._v_pad,
+                             n_pad, f["begin"], f["end"], sizes, [float(self.lrs[k]) for k, _ in GROUPS], 0.9, 0.999, 1e-15,
+                             self.step, f["loss"], f["skipped"])
+        f["h_grad"].barrier(channel=1)                   # every rank's broadcast has landed; gradients may be rewritten
+        return f["loss"][0]
 
     # ---- capacity mode bookkeeping -------------------------------------------------------------------------------
     def enable_async_binning(self, on: bool = True, margin: float = 1.2) -> None:
@@ -117,6 +187,7 @@ class RefineState:
         self.flat, self.exp_avg, self.exp_avg_sq = flat, exp_avg, exp_avg_sq
         self.grad = torch.zeros(n, device=self.device, dtype=torch.float32)
         self._r_seen = {}             # instance counts of the old Gaussian set say nothing about the new one
+        self.fused = None             # the symmetric buffers had the old size: call enable_fused_exchange again
         off = 0
         for name, k in GROUPS:
             self.slices[name] = (off, off + P * k, k)
@@ -255,6 +326,9 @@ def refine_iteration(state: RefineState, settings: MultiViewSettings, gt: torch.
             state.track_status(Vl)               # capacity mode: the count is looked at later, without a sync
         guarded = cap != 0
         state.last_guarded = guarded
+        if state.fused is not None and do_step and group is not None and state.fused["group"] is group:
+            loss = state.fused_exchange_step(loss, guarded)
+            return IterationResult(loss, int(R), radii, g2d)
         if guarded and group is not None and torch.distributed.get_world_size(group) > 1:
             # one rank's overflow must skip the step on EVERY rank: fold the flag into the exchange
             torch.distributed.all_reduce(state.status[1:2], op=torch.distributed.ReduceOp.MAX, group=group)

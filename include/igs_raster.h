@@ -258,6 +258,23 @@ int igs_depth_normal_loss(int use_coord, const float* map0, const float* map1, c
                           float* loss_sum, float* dL_dmap0, float* dL_dmap1, float* dL_dnormal, igs_alloc_fn temp_alloc,
                           void* temp_user, void* stream);
 
+/* The exchange step of the view-sharded refine iteration as ONE kernel over NVLink / NVSwitch multicast (no counterpart
+ * in the reference, which has no multi-GPU refine path; it replaces ncclAllReduce + the replicated Adam step of
+ * BASELINE's schedule).  Rank r owns floats [begin, end) of the packed record of n floats; for them the kernel
+ * reduces the gradient over all ranks with multimem.ld_reduce (grad_mc: MULTICAST address of the symmetric gradient
+ * buffers), applies the Adam step of igs_adam_step_groups (same arithmetic; exp_avg / exp_avg_sq are touched in [begin,
+ * end) only) to `param` (this rank's own parameter buffer) and broadcasts the result with multimem.st (param_mc:
+ * MULTICAST address of the symmetric parameter buffers).  The 4 floats at grad[n .. n+4) of every rank hold {partial
+ * loss, 1.0f if this rank's forward overflowed its instance capacity else 0, 0, 0}: *loss_out receives the sum of the
+ * partial losses, *skipped_out is 1 if any rank overflowed — then NO rank updates anything.  n, begin, end: multiples
+ * of 4; all buffers 16-byte aligned.  The caller orders the ranks: every rank's gradients (and tail slot) must be
+ * complete before any rank launches, and all launches complete before parameters are read or gradients rewritten
+ * (a cross-rank stream barrier before and after; igs_b200/refine.py uses the symmetric-memory signal pads). */
+int igs_fused_reduce_adam(const float* grad_mc, float* param_mc, const float* param, float* exp_avg, float* exp_avg_sq,
+                          size_t n, size_t begin, size_t end, int ngroups, const size_t* sizes, const float* lrs,
+                          float beta1, float beta2, float eps, int step, float* loss_out, unsigned int* skipped_out,
+                          void* stream);
+
 /* igs_depth_normal_loss for callers that cannot allocate (CUDA-graph capture, tight serving loops, harnesses that
  * forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.  Same arguments,
  * arithmetic and results as igs_depth_normal_loss, minus the allocator callback: the scratch (one double per 32x8-pixel
