@@ -66,29 +66,48 @@ fused_reduce_adam_kernel(const float* __restrict__ grad_mc, float* __restrict__ 
   }
   __syncthreads();
   if (s_tail[1] > 0.0f) return;   // some rank's forward overflowed its capacity: nobody steps (same decision everywhere)
+  // Four independent 16-byte items per thread and trip: the reduce is a round trip through the switch (microseconds),
+  // so the loads of all four are issued before the first is used.
+  constexpr int U = 4;
   const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-  for (unsigned long long i4 = begin4 + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i4 < end4; i4 += stride) {
-    const unsigned long long i = 4ull * i4;
-    const float4 g = multimem_ld_reduce_add(grad_mc + i);
-    float4 p = *reinterpret_cast<const float4*>(param + i);
-    float4 mm = *reinterpret_cast<const float4*>(m + i);
-    float4 vv = *reinterpret_cast<const float4*>(v + i);
-    float ss[4];
+  for (unsigned long long base4 = begin4 + (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; base4 < end4; base4 += U * stride) {
+    float4 g[U], p[U], mm[U], vv[U];
 #pragma unroll
-    for (int c = 0; c < 4; c++) {   // group boundaries need not be multiples of four
-      float s = gr.step_size[0];
-#pragma unroll
-      for (int k = 1; k < 8; k++)
-        if (k < gr.n && i + c >= gr.end[k - 1]) s = gr.step_size[k];
-      ss[c] = s;
+    for (int u = 0; u < U; u++) {
+      const unsigned long long i4 = base4 + u * stride;
+      if (i4 < end4) g[u] = multimem_ld_reduce_add(grad_mc + 4ull * i4);
     }
-    p.x = adam_one(p.x, g.x, mm.x, vv.x, ss[0], b1, b2, eps, inv_sqrt_bc2);
-    p.y = adam_one(p.y, g.y, mm.y, vv.y, ss[1], b1, b2, eps, inv_sqrt_bc2);
-    p.z = adam_one(p.z, g.z, mm.z, vv.z, ss[2], b1, b2, eps, inv_sqrt_bc2);
-    p.w = adam_one(p.w, g.w, mm.w, vv.w, ss[3], b1, b2, eps, inv_sqrt_bc2);
-    *reinterpret_cast<float4*>(m + i) = mm;
-    *reinterpret_cast<float4*>(v + i) = vv;
-    multimem_st(param_mc + i, p);
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const unsigned long long i4 = base4 + u * stride;
+      if (i4 < end4) {
+        p[u] = *reinterpret_cast<const float4*>(param + 4ull * i4);
+        mm[u] = *reinterpret_cast<const float4*>(m + 4ull * i4);
+        vv[u] = *reinterpret_cast<const float4*>(v + 4ull * i4);
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < U; u++) {
+      const unsigned long long i4 = base4 + u * stride;
+      if (i4 >= end4) continue;
+      const unsigned long long i = 4ull * i4;
+      float ss[4];
+#pragma unroll
+      for (int c = 0; c < 4; c++) {   // group boundaries need not be multiples of four
+        float sz = gr.step_size[0];
+#pragma unroll
+        for (int k = 1; k < 8; k++)
+          if (k < gr.n && i + c >= gr.end[k - 1]) sz = gr.step_size[k];
+        ss[c] = sz;
+      }
+      p[u].x = adam_one(p[u].x, g[u].x, mm[u].x, vv[u].x, ss[0], b1, b2, eps, inv_sqrt_bc2);
+      p[u].y = adam_one(p[u].y, g[u].y, mm[u].y, vv[u].y, ss[1], b1, b2, eps, inv_sqrt_bc2);
+      p[u].z = adam_one(p[u].z, g[u].z, mm[u].z, vv[u].z, ss[2], b1, b2, eps, inv_sqrt_bc2);
+      p[u].w = adam_one(p[u].w, g[u].w, mm[u].w, vv[u].w, ss[3], b1, b2, eps, inv_sqrt_bc2);
+      *reinterpret_cast<float4*>(m + i) = mm[u];
+      *reinterpret_cast<float4*>(v + i) = vv[u];
+      multimem_st(param_mc + i, p[u]);
+    }
   }
 }
 
@@ -124,7 +143,7 @@ extern "C" int igs_fused_reduce_adam(const float* grad_mc, float* param_mc, cons
   }
   if (off != n) { set_error("group sizes must add up to n"); return IGS_ERR_INVALID; }
   const size_t n4 = (end - begin) / 4;
-  size_t nb = (n4 + 255) / 256;
+  size_t nb = (n4 + 4 * 256 - 1) / (4 * 256);   // four items per thread
   if (nb > 148 * 8) nb = 148 * 8;
   if (nb == 0) nb = 1;   // the tail slot is still reduced (loss / overflow flag)
   count_launch();
