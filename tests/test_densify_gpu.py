@@ -116,3 +116,30 @@ def test_kernels_match_the_reference_class(cuda_dev, native, case):
                                        plan.samples.to(cuda_dev), float(plan.split_div), densify._offsets(P), densify._offsets(P_new))
     st.resize(P_new, flat, m, v)
     _check_against_golden(st, g)
+
+
+def test_batched_step_accumulates_the_same_statistics_as_single_view_steps(cuda_dev, native):
+    """The reference feeds add_densification_stats the gradient of ONE view's undivided loss (infer_batch.py:302-313).
+    A V-view step divides its loss by V; with grad_scale = V the accumulated statistics equal those of V single-view
+    steps at the same parameters, so densify_grad_threshold keeps its meaning under the batched schedule."""
+    from igs_b200 import densify, refine, scenes
+    from igs_b200.multiview import MultiViewSettings
+    from igs_b200.stream import select_views
+    P, V, W, H = 6000, 3, 160, 120
+    sc = scenes.make_gaussians(P, 0, -1.8)
+    cams = scenes.make_cameras(V, W, H, 1)
+    st = MultiViewSettings(H, W, cams.tanfovx, cams.tanfovy, 0.0, torch.zeros(3, device=cuda_dev), 1.0,
+                           cams.viewmatrix.to(cuda_dev).contiguous(), cams.projmatrix.to(cuda_dev).contiguous(), 3,
+                           cams.campos.to(cuda_dev).contiguous())
+    gt = torch.rand(V, 3, H, W, generator=torch.Generator().manual_seed(9)).to(cuda_dev)
+    state = refine.RefineState(sc.xyz, sc.log_scale, sc.rot, sc.opacity_logit, sc.sh, cuda_dev)
+    a = densify.DensifyStats(P, cuda_dev)
+    r = refine.refine_iteration(state, st, gt, V, do_step=False)
+    a.update(r.grad_means2D, r.radii, grad_scale=float(V))
+    b = densify.DensifyStats(P, cuda_dev)
+    for v in range(V):
+        r1 = refine.refine_iteration(state, select_views(st, [v]), gt[v:v + 1], 1, do_step=False)
+        b.update(r1.grad_means2D, r1.radii)
+    assert torch.equal(a.denom, b.denom) and torch.equal(a.max_radii2D, b.max_radii2D)
+    assert float(a.denom.max()) == V
+    assert torch.allclose(a.grad_accum, b.grad_accum, rtol=1e-4, atol=1e-6 * float(b.grad_accum.max()))
