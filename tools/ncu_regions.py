@@ -1,21 +1,25 @@
 #!/usr/bin/env python
 """Groups the SASS of the first kernel in an ncu report (--import-source on) into regions of equal execution count and
 prints instructions, stall samples and shared wavefronts per region; with --top also the most-sampled instructions.
-usage: python tools/ncu_regions.py report.ncu-rep [--top N] [--dump a:b]"""
+usage: python tools/ncu_regions.py report.ncu-rep [--kernel substr] [--top N] [--dump a:b]"""
 import csv, io, subprocess, sys
 from collections import Counter
 
 rep = sys.argv[1]
 out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
 rows = list(csv.reader(io.StringIO(out)))
-print(rows[0][1][:120])
-hdr = rows[1]
+# several kernels in one report: blocks start with a ["Kernel Name", name] row followed by a header row; keep the first
+# block, or the last one whose name contains the --kernel substring
+starts = [k for k, r in enumerate(rows) if r and r[0] == "Kernel Name"]
+pick = starts[0]
+if "--kernel" in sys.argv:
+    want = sys.argv[sys.argv.index("--kernel") + 1]
+    pick = [k for k in starts if want in rows[k][1]][-1]
+print(rows[pick][1][:120])
+hdr = rows[pick + 1]
 iS, iI, iSm, iW, iT = (hdr.index(x) for x in ("Source", "Instructions Executed", "# Samples", "L1 Wavefronts Shared", "Avg. Threads Executed"))
-body = rows[2:]
-for k, r in enumerate(body):   # several kernels in one report: keep the first (or the one selected with --kernel N)
-    if r and r[0] == "Kernel Name":
-        body = body[:k]
-        break
+nxt = [k for k in starts if k > pick]
+body = rows[pick + 2:(nxt[0] if nxt else len(rows))]
 lines = [(int(r[iI]), int(r[iSm]), int(r[iW]), r[iS].strip(), r[iT]) for r in body if len(r) > iW]
 tot = sum(l[0] for l in lines); ts = sum(l[1] for l in lines)
 print(f"total warp instructions {tot/1e9:.3f} G, samples {ts}, shared wavefronts {sum(l[2] for l in lines)/1e9:.3f} G")
