@@ -24,6 +24,13 @@ namespace igs {
 #define LOSS_TH (LOSS_BY + 2 * LOSS_R)  // 42 rows: tile + halo
 #define LOSS_TC 48                      // staged columns: x0-8 .. x0+39 (16-B aligned superset of the 42-column halo)
 #define LOSS_X0 8                       // staged column of image column x0
+// Row strides in shared memory are chosen for the 16-byte accesses of the horizontal pass.  A quarter-warp (the unit a
+// 16-byte shared access is served in) covers column groups {0..3} (or {4..7}) of TWO adjacent rows (loss_htask); its
+// eight 16-byte chunks fall into eight different 16-byte bank groups when the row stride is an ODD number of chunks for
+// the pair tiles (adjacent column groups are 2 chunks apart) and 4 mod 8 chunks for the scalar tiles (1 chunk apart).
+// ncu r02: the unpadded 48 / 32-column rows made every such access a 2-way conflict (35-39 % of all wavefronts).
+#define LOSS_TCP 50                     // staged pair tiles: 48 columns + 2 pad = 25 chunks
+#define LOSS_HP 34                      // horizontally filtered pair tiles: 32 columns + 2 pad = 17 chunks
 
 struct LossParams {
   int planes, H, W;        // planes = V*3
@@ -33,9 +40,8 @@ struct LossParams {
   float inv_n;             // grad_scale / (3*H*W)
   const float* pred;
   const float* gt;
-  float* dmu1;             // scratch [planes][H][W]
-  float* dE11;
-  float* dE12;
+  float2* d01;             // scratch [planes][H][W] pairs (dS/dmu1, dS/dE11): pass 2 copies them straight into shared memory
+  float* dE12;             // scratch [planes][H][W]
   float* dpred;
   double* partial;         // [gridDim.x*gridDim.y*gridDim.z]
   // Optional per-view pixel-row ranges: the loss of view v is summed over rows [rows[2v], rows[2v+1]) only (a rank
@@ -82,23 +88,45 @@ __device__ __forceinline__ void store4_pairs(float2* dst, const f32x2 (&o)[4]) {
   *reinterpret_cast<float4*>(dst + 2) = make_float4(a, b, c, d);
 }
 
+// Horizontal-pass task t -> (row r, column group cg of 4 outputs): lanes 0-3 / 4-7 of a quarter-warp take column groups
+// {0..3} (or {4..7}) of rows 2k / 2k+1 (see the stride note above).  t < LOSS_TH * 8.
+__device__ __forceinline__ void loss_htask(int t, int& r, int& cg) {
+  cg = (t & 3) | ((t >> 1) & 4);
+  r = ((t >> 4) << 1) | ((t >> 2) & 1);
+}
+
 // Stage rows [y0-5, y0+37) x columns [x0-8, x0+40) of two planes A, B as interleaved pairs (zero outside the image).
 template <bool VEC>
-__device__ __forceinline__ void stage_pairs(float2 (*dst)[LOSS_TC], const float* __restrict__ A,
+__device__ __forceinline__ void stage_pairs(float2 (*dst)[LOSS_TCP], const float* __restrict__ A,
                                             const float* __restrict__ B, int x0, int y0, int W, int H, int tid) {
   if constexpr (VEC) {
-    for (int t = tid; t < LOSS_TH * (LOSS_TC / 4); t += 256) {
+    // both iterations' loads are issued before the first store: one DRAM round trip per CTA instead of two
+    constexpr int NT = LOSS_TH * (LOSS_TC / 4);
+    float4 a[2], b[2];
+#pragma unroll
+    for (int it = 0; it < 2; it++) {
+      const int t = tid + it * 256;
       const int ty = t / (LOSS_TC / 4), g = t - ty * (LOSS_TC / 4);
       const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + 4 * g;
-      float4 a = make_float4(0, 0, 0, 0), b = a;
-      if (gy >= 0 && gy < H && gx >= 0 && gx < W) {
+      a[it] = make_float4(0, 0, 0, 0); b[it] = a[it];
+      if (t < NT && gy >= 0 && gy < H && gx >= 0 && gx < W) {
         const uint32_t o = (uint32_t)gy * (uint32_t)W + (uint32_t)gx;
-        a = *reinterpret_cast<const float4*>(A + o);
-        b = *reinterpret_cast<const float4*>(B + o);
+        a[it] = *reinterpret_cast<const float4*>(A + o);
+        b[it] = *reinterpret_cast<const float4*>(B + o);
       }
+    }
+#pragma unroll
+    for (int it = 0; it < 2; it++) {
+      const int t = tid + it * 256;
+      if (t >= NT) break;
+      const int ty = t / (LOSS_TC / 4), g = t - ty * (LOSS_TC / 4);
       float4* d = reinterpret_cast<float4*>(&dst[ty][4 * g]);
-      d[0] = make_float4(a.x, b.x, a.y, b.y);
-      d[1] = make_float4(a.z, b.z, a.w, b.w);
+      const float4 lo = make_float4(a[it].x, b[it].x, a[it].y, b[it].y), hi = make_float4(a[it].z, b[it].z, a[it].w, b[it].w);
+      // a quarter-warp's eight threads are 2 chunks apart: the upper four store their second chunk first, so the eight
+      // stores of one instruction hit eight different bank groups
+      const int sw = (g >> 2) & 1;
+      d[sw] = sw ? hi : lo;
+      d[sw ^ 1] = sw ? lo : hi;
     }
   } else {
     for (int t = tid; t < LOSS_TH * LOSS_TC; t += 256) {
@@ -110,23 +138,35 @@ __device__ __forceinline__ void stage_pairs(float2 (*dst)[LOSS_TC], const float*
     }
   }
 }
+// Pass 2: stage the same window of the partials — pairs D = (dS/dmu1, dS/dE11) and the scalar plane E = dS/dE12.
+// VEC: asynchronous 16-byte global -> shared copies (cp.async, zero-filled outside the image): nothing passes through
+// registers and all of a thread's six copies are in flight at once (ncu r02: the register-staged loop made this kernel
+// latency bound — long-scoreboard 14.5 stalled warps per issue, 40 % issue utilisation).
 template <bool VEC>
-__device__ __forceinline__ void stage_scalar(float (*dst)[LOSS_TC], const float* __restrict__ A, int x0, int y0, int W,
-                                             int H, int tid) {
+__device__ __forceinline__ void stage_partials(float2 (*dp)[LOSS_TCP], float (*ds)[LOSS_TC], const float2* __restrict__ D,
+                                               const float* __restrict__ E, int x0, int y0, int W, int H, int tid) {
   if constexpr (VEC) {
-    for (int t = tid; t < LOSS_TH * (LOSS_TC / 4); t += 256) {
+    for (int t = tid; t < LOSS_TH * (LOSS_TC / 2); t += 256) {   // 16 bytes = 2 pairs
+      const int ty = t / (LOSS_TC / 2), g = t - ty * (LOSS_TC / 2);
+      const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + 2 * g;
+      const bool ok = gy >= 0 && gy < H && gx >= 0 && gx < W;
+      cp_async16_zfill(smem_addr(&dp[ty][2 * g]), D + (ok ? (uint32_t)gy * (uint32_t)W + (uint32_t)gx : 0u), ok);
+    }
+    for (int t = tid; t < LOSS_TH * (LOSS_TC / 4); t += 256) {   // 16 bytes = 4 scalars
       const int ty = t / (LOSS_TC / 4), g = t - ty * (LOSS_TC / 4);
       const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + 4 * g;
-      float4 a = make_float4(0, 0, 0, 0);
-      if (gy >= 0 && gy < H && gx >= 0 && gx < W) a = *reinterpret_cast<const float4*>(A + (uint32_t)gy * (uint32_t)W + (uint32_t)gx);
-      *reinterpret_cast<float4*>(&dst[ty][4 * g]) = a;
+      const bool ok = gy >= 0 && gy < H && gx >= 0 && gx < W;
+      cp_async16_zfill(smem_addr(&ds[ty][4 * g]), E + (ok ? (uint32_t)gy * (uint32_t)W + (uint32_t)gx : 0u), ok);
     }
+    cp_async_commit();
   } else {
     for (int t = tid; t < LOSS_TH * LOSS_TC; t += 256) {
       const int ty = t / LOSS_TC, tx = t - ty * LOSS_TC;
       const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + tx;
       const bool ok = gy >= 0 && gy < H && gx >= 0 && gx < W;
-      dst[ty][tx] = ok ? A[(uint32_t)gy * (uint32_t)W + (uint32_t)gx] : 0.0f;
+      const uint32_t o = ok ? (uint32_t)gy * (uint32_t)W + (uint32_t)gx : 0u;
+      dp[ty][tx] = ok ? D[o] : make_float2(0.0f, 0.0f);
+      ds[ty][tx] = ok ? E[o] : 0.0f;
     }
   }
 }
@@ -134,10 +174,10 @@ __device__ __forceinline__ void stage_scalar(float (*dst)[LOSS_TC], const float*
 template <bool VEC>
 __global__ void __launch_bounds__(256)
 loss_pass1_kernel(LossParams p) {
-  __shared__ __align__(16) float2 sxy[LOSS_TH][LOSS_TC];           // (pred, gt)
-  __shared__ __align__(16) float2 hbA[LOSS_TH][LOSS_BX];           // horizontally filtered (x, y)
-  __shared__ __align__(16) float2 hbB[LOSS_TH][LOSS_BX];           // (x^2, y^2)
-  __shared__ __align__(16) float hbC[LOSS_TH][LOSS_BX];            // x y
+  __shared__ __align__(16) float2 sxy[LOSS_TH][LOSS_TCP];          // (pred, gt)
+  __shared__ __align__(16) float2 hbA[LOSS_TH][LOSS_HP];           // horizontally filtered (x, y)
+  __shared__ __align__(16) float2 hbB[LOSS_TH][LOSS_HP];           // (x^2, y^2)
+  __shared__ __align__(16) float hbC[LOSS_TH][LOSS_BX];            // x y; odd rows with the two 16-column halves swapped
   __shared__ double red[8];
   const int plane = blockIdx.z;
   const size_t po = (size_t)plane * p.H * p.W;
@@ -157,7 +197,8 @@ loss_pass1_kernel(LossParams p) {
   // horizontal: task = (row r, column group cg of 4 outputs); taps of output column 4cg+j are staged columns
   // 4cg+3+j .. 4cg+13+j = v[1+j .. 11+j] of the 16 pairs loaded from the (16-B aligned) column 4cg+2
   for (int t = tid; t < LOSS_TH * (LOSS_BX / 4); t += 256) {
-    const int r = t / (LOSS_BX / 4), cg = t - r * (LOSS_BX / 4);
+    int r, cg;
+    loss_htask(t, r, cg);
     f32x2 v[16], sq[16];
     float pr[16];
     load16_pairs(&sxy[r][cg * 4 + 2], v);
@@ -184,7 +225,7 @@ loss_pass1_kernel(LossParams p) {
     }
     store4_pairs(&hbA[r][cg * 4], oA);
     store4_pairs(&hbB[r][cg * 4], oB);
-    *reinterpret_cast<float4*>(&hbC[r][cg * 4]) = make_float4(oC[0], oC[1], oC[2], oC[3]);
+    *reinterpret_cast<float4*>(&hbC[r][(cg ^ ((r & 1) << 2)) * 4]) = make_float4(oC[0], oC[1], oC[2], oC[3]);
   }
   __syncthreads();
   // vertical + SSIM + partials: task = (column c, row group rg of 4 outputs), all 256 threads
@@ -216,7 +257,7 @@ loss_pass1_kernel(LossParams p) {
       }
       float ins[14];
 #pragma unroll
-      for (int k = 0; k < 14; k++) ins[k] = hbC[rg * 4 + k][c];
+      for (int k = 0; k < 14; k++) ins[k] = hbC[rg * 4 + k][c ^ ((k & 1) << 4)];   // (row parity = k parity)
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         float a = 0.0f;
@@ -227,8 +268,7 @@ loss_pass1_kernel(LossParams p) {
     }
     const int gx = x0 + c;
     float accf = 0.0f;
-    float* __restrict__ o_mu = p.dmu1 + po;
-    float* __restrict__ o_11 = p.dE11 + po;
+    float2* __restrict__ o_01 = p.d01 + po;
     float* __restrict__ o_12 = p.dE12 + po;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
@@ -248,7 +288,7 @@ loss_pass1_kernel(LossParams p) {
       const float d11 = -ssim * Cc * inv;
       const float d12 = 2.0f * A * inv;
       const uint32_t o = (uint32_t)gy * (uint32_t)p.W + (uint32_t)gx;
-      o_mu[o] = dmu1; o_11[o] = d11; o_12[o] = d12;
+      o_01[o] = make_float2(dmu1, d11); o_12[o] = d12;
       const float2 xy = sxy[rg * 4 + j + LOSS_R][c + LOSS_X0];
       accf += p.lambda * fabsf(xy.x - xy.y) - (1.0f - p.lambda) * ssim;   // four pixels in fp32, then double
     }
@@ -269,10 +309,10 @@ loss_pass1_kernel(LossParams p) {
 template <bool VEC>
 __global__ void __launch_bounds__(256)
 loss_pass2_kernel(LossParams p) {
-  __shared__ __align__(16) float2 s01[LOSS_TH][LOSS_TC];           // (dS/dmu1, dS/dE11)
-  __shared__ __align__(16) float s2[LOSS_TH][LOSS_TC];             // dS/dE12
-  __shared__ __align__(16) float2 hb01[LOSS_TH][LOSS_BX];
-  __shared__ __align__(16) float hb2[LOSS_TH][LOSS_BX];
+  __shared__ __align__(16) float2 s01[LOSS_TH][LOSS_TCP];          // (dS/dmu1, dS/dE11)
+  __shared__ __align__(16) float s2[LOSS_TH][LOSS_TC];             // dS/dE12 (48 columns = 12 chunks: 4 mod 8)
+  __shared__ __align__(16) float2 hb01[LOSS_TH][LOSS_HP];
+  __shared__ __align__(16) float hb2[LOSS_TH][LOSS_BX];            // odd rows with the two 16-column halves swapped
   const int plane = blockIdx.z;
   const size_t po = (size_t)plane * p.H * p.W;
   const int x0 = blockIdx.x * LOSS_BX, y0 = blockIdx.y * LOSS_BY;
@@ -280,14 +320,15 @@ loss_pass2_kernel(LossParams p) {
   int r0, r1;
   loss_row_range(p, plane, r0, r1);
   if (y0 >= r1 + LOSS_R || y0 + LOSS_BY <= r0 - LOSS_R) return;  // dL/dpred is zero here (pre-filled by the launcher)
-  stage_pairs<VEC>(s01, p.dmu1 + po, p.dE11 + po, x0, y0, p.W, p.H, tid);
-  stage_scalar<VEC>(s2, p.dE12 + po, x0, y0, p.W, p.H, tid);
+  stage_partials<VEC>(s01, s2, p.d01 + po, p.dE12 + po, x0, y0, p.W, p.H, tid);
+  if constexpr (VEC) cp_async_wait_all();
   __syncthreads();
   f32x2 w2[11];
 #pragma unroll
   for (int k = 0; k < 11; k++) w2[k] = pack2(p.win[k], p.win[k]);
   for (int t = tid; t < LOSS_TH * (LOSS_BX / 4); t += 256) {
-    const int r = t / (LOSS_BX / 4), cg = t - r * (LOSS_BX / 4);
+    int r, cg;
+    loss_htask(t, r, cg);
     f32x2 v[16];
     float u[20];
     load16_pairs(&s01[r][cg * 4 + 2], v);  // taps of output column 4cg+j: v[1+j .. 11+j]
@@ -306,11 +347,28 @@ loss_pass2_kernel(LossParams p) {
       o01[j] = a; o2[j] = c;
     }
     store4_pairs(&hb01[r][cg * 4], o01);
-    *reinterpret_cast<float4*>(&hb2[r][cg * 4]) = make_float4(o2[0], o2[1], o2[2], o2[3]);
+    *reinterpret_cast<float4*>(&hb2[r][(cg ^ ((r & 1) << 2)) * 4]) = make_float4(o2[0], o2[1], o2[2], o2[3]);
   }
   __syncthreads();
   {
     const int c = tid % LOSS_BX, rg = tid / LOSS_BX;
+    const int gx = x0 + c;
+    // The staged partials are dead now: this thread's four (pred, gt) values are copied into that space asynchronously
+    // (each thread copies, waits for and reads only its own words), so their DRAM latency overlaps the vertical filter.
+    float* const xy = reinterpret_cast<float*>(&s01[0][0]) + tid * 8;
+    {
+      const float* __restrict__ X = p.pred + po;
+      const float* __restrict__ Y = p.gt + po;
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const int gy = y0 + rg * 4 + j;
+        if (gx >= p.W || gy >= p.H) continue;
+        const uint32_t o = (uint32_t)gy * (uint32_t)p.W + (uint32_t)gx;
+        cp_async4(smem_addr(xy + 2 * j), X + o);
+        cp_async4(smem_addr(xy + 2 * j + 1), Y + o);
+      }
+      cp_async_commit();
+    }
     f32x2 m01[4];
     float m2[4];
     {
@@ -326,7 +384,7 @@ loss_pass2_kernel(LossParams p) {
       }
       float ins[14];
 #pragma unroll
-      for (int k = 0; k < 14; k++) ins[k] = hb2[rg * 4 + k][c];
+      for (int k = 0; k < 14; k++) ins[k] = hb2[rg * 4 + k][c ^ ((k & 1) << 4)];   // (row parity = k parity)
 #pragma unroll
       for (int j = 0; j < 4; j++) {
         float a = 0.0f;
@@ -335,16 +393,15 @@ loss_pass2_kernel(LossParams p) {
         m2[j] = a;
       }
     }
-    const int gx = x0 + c;
-    const float* __restrict__ X = p.pred + po;
-    const float* __restrict__ Y = p.gt + po;
+    cp_async_wait_all();
     float* __restrict__ O = p.dpred + po;
 #pragma unroll
     for (int j = 0; j < 4; j++) {
       const int gy = y0 + rg * 4 + j;
       if (gx >= p.W || gy >= p.H) continue;
       const uint32_t o = (uint32_t)gy * (uint32_t)p.W + (uint32_t)gx;
-      const float xv = X[o], yv = Y[o];
+      const float2 v = *reinterpret_cast<const float2*>(xy + 2 * j);
+      const float xv = v.x, yv = v.y;
       float g0, g1;
       unpack2(m01[j], g0, g1);
       const float dssim = g0 + 2.0f * xv * g1 + yv * m2[j];
@@ -415,20 +472,19 @@ void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W,
   p.inv_n = grad_scale / (3.0f * (float)H * (float)W);  // only dL_dpred uses it; the loss value is finished in double
   p.pred = pred; p.gt = gt; p.dpred = dpred;
   const size_t N = (size_t)H * W, planes = (size_t)(by_view ? 1 : V) * 3;
-  p.dmu1 = reinterpret_cast<float*>(scratch);
-  p.dE11 = p.dmu1 + planes * N;
-  p.dE12 = p.dE11 + planes * N;
+  p.d01 = reinterpret_cast<float2*>(scratch);
+  p.dE12 = reinterpret_cast<float*>(scratch) + 2 * planes * N;
   size_t off = (3 * planes * N * sizeof(float) + 255) & ~size_t(255);
   p.partial = reinterpret_cast<double*>(scratch + off);
   if ((size_t)H * W >= (1ull << 32)) return;  // in-plane offsets are 32-bit (igs_refine_loss rejects such sizes)
   // 16-byte staging loads need W % 4 == 0 (every float4 entirely inside or outside the image) and aligned planes
   const bool vec = (W % 4 == 0) && ((reinterpret_cast<uintptr_t>(pred) | reinterpret_cast<uintptr_t>(gt) |
-                                     reinterpret_cast<uintptr_t>(p.dmu1)) % 16 == 0) && ((size_t)H * W < (1ull << 31));
+                                     reinterpret_cast<uintptr_t>(p.d01)) % 16 == 0) && ((size_t)H * W < (1ull << 31));
   const dim3 grid_all((W + LOSS_BX - 1) / LOSS_BX, (H + LOSS_BY - 1) / LOSS_BY, V * 3);
   const size_t nblk = (size_t)grid_all.x * grid_all.y * grid_all.z;
   if (p.has_rows) cudaMemsetAsync(dpred, 0, (size_t)V * 3 * N * sizeof(float), s);   // rows nobody here owns
   if (!by_view) {
-    if (p.has_rows) cudaMemsetAsync(p.dmu1, 0, 3 * planes * N * sizeof(float), s);    // (pass 2 reads a 5-row halo of them)
+    if (p.has_rows) cudaMemsetAsync(p.d01, 0, 3 * planes * N * sizeof(float), s);     // (pass 2 reads a 5-row halo of them)
     count_launch(2);
     if (vec) {
       loss_pass1_kernel<true><<<grid_all, 256, 0, s>>>(p);
@@ -447,7 +503,7 @@ void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W,
       q.partial = p.partial + (size_t)v * nblk_view;
       if (p.has_rows) {
         q.rows[0] = p.rows[2 * v]; q.rows[1] = p.rows[2 * v + 1];
-        cudaMemsetAsync(q.dmu1, 0, 9 * N * sizeof(float), s);   // the previous view's partials, outside this view's rows
+        cudaMemsetAsync(q.d01, 0, 9 * N * sizeof(float), s);    // the previous view's partials, outside this view's rows
       }
       count_launch(2);
       if (vec) {
