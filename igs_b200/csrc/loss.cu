@@ -355,7 +355,7 @@ loss_pass2_kernel(LossParams p) {
     const int gx = x0 + c;
     // The staged partials are dead now: this thread's four (pred, gt) values are copied into that space asynchronously
     // (each thread copies, waits for and reads only its own words), so their DRAM latency overlaps the vertical filter.
-    float* const xy = reinterpret_cast<float*>(&s01[0][0]) + tid * 8;
+    float* const xy = reinterpret_cast<float*>(&s01[0][0]) + tid;   // word k of this thread at xy[256 k] (conflict-free)
     {
       const float* __restrict__ X = p.pred + po;
       const float* __restrict__ Y = p.gt + po;
@@ -364,8 +364,8 @@ loss_pass2_kernel(LossParams p) {
         const int gy = y0 + rg * 4 + j;
         if (gx >= p.W || gy >= p.H) continue;
         const uint32_t o = (uint32_t)gy * (uint32_t)p.W + (uint32_t)gx;
-        cp_async4(smem_addr(xy + 2 * j), X + o);
-        cp_async4(smem_addr(xy + 2 * j + 1), Y + o);
+        cp_async4(smem_addr(xy + 256 * (2 * j)), X + o);
+        cp_async4(smem_addr(xy + 256 * (2 * j + 1)), Y + o);
       }
       cp_async_commit();
     }
@@ -400,8 +400,7 @@ loss_pass2_kernel(LossParams p) {
       const int gy = y0 + rg * 4 + j;
       if (gx >= p.W || gy >= p.H) continue;
       const uint32_t o = (uint32_t)gy * (uint32_t)p.W + (uint32_t)gx;
-      const float2 v = *reinterpret_cast<const float2*>(xy + 2 * j);
-      const float xv = v.x, yv = v.y;
+      const float xv = xy[256 * (2 * j)], yv = xy[256 * (2 * j + 1)];
       float g0, g1;
       unpack2(m01[j], g0, g1);
       const float dssim = g0 + 2.0f * xv * g1 + yv * m2[j];
