@@ -479,10 +479,14 @@ blend_bwd2_kernel(BlendBwdParams p) {
   __shared__ uint32_t s_rawe[BATCH];      //   emission slot
   __shared__ uint32_t s_e[2 * BATCH];     // emission slots of the batch, double-buffered (read by the previous batch's write-out)
   __shared__ uint8_t s_queue[8 * BATCH];  // per warp: shared-memory indices of the survivors that hit the warp's block
+  // inverse of the queues, double-buffered like s_e: byte [slot][w] = position of batch entry `slot` in warp w's queue
+  // (0xFF: the entry does not touch that warp's block).  The accumulator rows are indexed by QUEUE POSITION, so only
+  // rows that were written are ever read: no zero-fill, no clearing, and the write-out reads ~2 rows per entry, not 8.
+  __shared__ __align__(16) uint8_t s_inv[2 * BATCH * 8];
   __shared__ uint32_t s_wcount[8];
   __shared__ uint32_t s_red[8];
   extern __shared__ __align__(16) float s_dyn[];
-  float* s_acc = s_dyn;                                             // [8 warps][BATCH][AS]
+  float* s_acc = s_dyn;                                             // [8 warps][BATCH queue positions][AS]
   float* s_stage = s_dyn + 8 * BATCH * AS;                          // [8 warps][G][33] float2 (aT, q)
   float4* s_pix = reinterpret_cast<float4*>(s_stage + 8 * G * BWD2_STRIDE * 2);  // [8 warps][34] {dLp r, g, b, -}
 
@@ -519,7 +523,6 @@ blend_bwd2_kernel(BlendBwdParams p) {
   const uint32_t rawh_addr = smem_addr(s_rawh) + threadIdx.x * 32;
   const uint32_t rawb_addr = smem_addr(s_rawb) + threadIdx.x * 4;
   const uint32_t rawe_addr = smem_addr(s_rawe) + threadIdx.x * 4;
-  for (uint32_t f = threadIdx.x; f < 8 * BATCH * AS; f += 256) s_acc[f] = 0.0f;
 
   const uint2 range = p.ranges[gt];
   const uint32_t last_contributor = inside ? p.n_contrib[(size_t)v * 2 * N + pix_id] : 0u;
@@ -599,6 +602,8 @@ blend_bwd2_kernel(BlendBwdParams p) {
     float4 ha, hb;
     float ex = 0, ey = 0, tau = 0, blue = 0;
     uint32_t* const e_cur = s_e + (parity ? BATCH : 0);
+    uint8_t* const inv_cur = s_inv + (parity ? BATCH * 8 : 0);
+    if (threadIdx.x < BATCH * 2) reinterpret_cast<uint32_t*>(inv_cur)[threadIdx.x] = 0xFFFFFFFFu;
     if (threadIdx.x < nb) {
       ha = lds128_at(rawh_addr);
       hb = lds128_at(rawh_addr + 16);
@@ -627,15 +632,21 @@ blend_bwd2_kernel(BlendBwdParams p) {
     for (uint32_t seg = 0; seg * 32 < nb; seg++) {
       const uint32_t k = seg * 32 + lane;
       bool hit = false;
+      uint32_t slot_of_k = 0;
       if ((uint32_t)lane < s_wcount[seg]) {
         const uint32_t ak = rec_base + k * 16;
         const float4 a = lds128<0>(ak);
         const float4 b = lds128<BATCH * 16>(ak);
         const float4 c = lds128<BATCH * 32>(ak);
+        slot_of_k = __float_as_uint(c.w);
         hit = (__float_as_uint(c.z) <= wlast) && block_can_contribute(a.x, a.y, a.z, a.w, b.x, c.y, bx0, by0, bx1, by1);
       }
       const uint32_t m = __ballot_sync(0xffffffffu, hit);
-      if (hit) queue[qn + __popc(m & ((1u << lane) - 1u))] = (uint8_t)k;
+      if (hit) {
+        const uint32_t pos = qn + __popc(m & ((1u << lane) - 1u));
+        queue[pos] = (uint8_t)k;
+        inv_cur[slot_of_k * 8u + (uint32_t)w] = (uint8_t)pos;
+      }
       qn += __popc(m);
     }
     __syncwarp();
@@ -674,7 +685,6 @@ blend_bwd2_kernel(BlendBwdParams p) {
       const uint32_t ak = rec_base + kj * 16;
       const float4 a = lds128<0>(ak);
       const float4 bq = lds128<BATCH * 16>(ak);
-      const float slot_bits = lds32<BATCH * 32 + 12>(ak);
       // Every per-Gaussian sum is linear in (aT, q) with coefficients that are polynomials of the pixel offset
       // d = centre - pixel.  With the pixel at column c, row r of this lane's half (d = (gx - c, gy - r)) the q-sums
       // expand into MOMENTS of q over the half, which need no per-pixel geometry at all:
@@ -726,7 +736,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
         // dL/dconic = -0.5 G d d^T dL/dG;  |grad| accumulates the per-pixel absolute values
         const float o = bq.y;
         const float mo = -o, ho = -0.5f * o;
-        const uint32_t aa = acc_base + __float_as_uint(slot_bits) * (uint32_t)(AS * 4);
+        const uint32_t aa = acc_base + (g0 + j) * (uint32_t)(AS * 4);
         sts128_at(aa, v0, v1, v2, mo * fmaf(a.z, a3, a.w * a4) * p.half_w);
         sts128_at(aa + 16, mo * fmaf(a.w, a3, bq.x * a4) * p.half_h, o * fmaf(p.half_w, b3, p.half_h * b4), ho * s6, ho * s7);
         sts64_at(aa + 32, ho * s8, v9);
@@ -741,17 +751,19 @@ blend_bwd2_kernel(BlendBwdParams p) {
       const uint32_t sl = f >> 2, q4 = f & 3;
       float4 sum = make_float4(0, 0, 0, 0);
       if (q4 < 3) {
+        const uint2 iv = *reinterpret_cast<const uint2*>(inv_cur + sl * 8u);
 #pragma unroll
-        for (int ww = 0; ww < 8; ww++) {
-          float4* pa = reinterpret_cast<float4*>(s_acc + ((size_t)ww * BATCH + sl) * AS) + q4;
-          const float4 x = *pa;
-          sum.x += x.x; sum.y += x.y; sum.z += x.z; sum.w += x.w;
-          *pa = make_float4(0, 0, 0, 0);
+        for (int ww = 0; ww < 8; ww++) {   // warp order, as before: absent rows were zeros then and are skipped now
+          const uint32_t qp = ((ww < 4 ? iv.x : iv.y) >> (8 * (ww & 3))) & 0xFFu;
+          if (qp != 0xFFu) {
+            const float4 x = reinterpret_cast<const float4*>(s_acc + ((size_t)ww * BATCH + qp) * AS)[q4];
+            sum.x += x.x; sum.y += x.y; sum.z += x.z; sum.w += x.w;
+          }
         }
       }
       reinterpret_cast<float4*>(p.grec + (size_t)e_cur[sl] * NS)[q4] = sum;
     }
-    // no barrier here: the next batch writes the OTHER half of s_e, and s_rec / s_acc only change hands at its barrier
+    // no barrier here: the next batch writes the OTHER halves of s_e / s_inv, and s_rec / s_acc only change hands at its barrier
     hi = lo;
     parity ^= 1u;
   }
