@@ -421,7 +421,7 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   }
 
   GatherBwdParams gp;
-  gp.P = P; gp.V = V; gp.W = W; gp.H = H; gp.ns = ns; gp.capacity = R; gp.focal_x = focal_x; gp.focal_y = focal_y;
+  gp.P = P; gp.V = V; gp.W = W; gp.H = H; gp.ns = ns; gp.capacity = R; gp.skip_geo = 0; gp.focal_x = focal_x; gp.focal_y = focal_y;
   gp.tan_fovx = a->tan_fovx; gp.tan_fovy = a->tan_fovy; gp.kernel_size = a->kernel_size;
   gp.means3D = a->means3D; gp.cams = G.cams; gp.cov3D = G.cov3D; gp.eig = G.eig; gp.head = G.head; gp.radii = G.radii;
   gp.tiles = G.tiles; gp.rank = G.rank; gp.sorted_gid = G.sval[(hv.flags >> 8) & 1]; gp.inst_off = G.inst_off; gp.clamped = G.clamped; gp.grec = grec; gp.sums = sums;

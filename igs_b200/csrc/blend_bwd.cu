@@ -466,13 +466,17 @@ __device__ __forceinline__ void sts128_at(uint32_t addr, float a, float b, float
   asm volatile("st.shared.v4.f32 [%0], {%1,%2,%3,%4};" ::"r"(addr), "f"(a), "f"(b), "f"(c), "f"(d) : "memory");
 }
 
-template <int BATCH, int MINB>
+// CAP = accumulator rows per warp (a multiple of the group size).  A warp whose queue for one batch is longer than CAP
+// works it off in rounds of CAP hits with a write-out after each (later rounds add to the record in global memory);
+// with CAP = BATCH there is exactly one round.  A smaller CAP buys a larger BATCH at the same shared-memory footprint.
+template <int BATCH, int MINB, int CAP>
 __global__ void __launch_bounds__(256, MINB)
 blend_bwd2_kernel(BlendBwdParams p) {
   constexpr int NS = 16;  // floats per gradient record in global memory
   constexpr int AS = 12;  // accumulator stride per batch slot (10 values + 2 pad words: 16-byte rows)
   constexpr int G = BWD2_GROUP;
   static_assert(BATCH <= 255 && BATCH % 32 == 0, "hit queue entries are bytes; whole 32-entry segments");
+  static_assert(CAP % BWD2_GROUP == 0 && CAP <= BATCH, "groups do not straddle rounds");
   __shared__ float4 s_rec[BATCH * 3];     // survivors: {x, y, conic.x, conic.y} {conic.z, opacity, r, g} {blue, tau, position, slot}
   __shared__ float4 s_rawh[BATCH * 2];    // cp.async landing zone of the NEXT batch: heads as fetched (entry t: thread t's)
   __shared__ float s_rawb[BATCH];         //   blue
@@ -486,8 +490,8 @@ blend_bwd2_kernel(BlendBwdParams p) {
   __shared__ uint32_t s_wcount[8];
   __shared__ uint32_t s_red[8];
   extern __shared__ __align__(16) float s_dyn[];
-  float* s_acc = s_dyn;                                             // [8 warps][BATCH queue positions][AS]
-  float* s_stage = s_dyn + 8 * BATCH * AS;                          // [8 warps][G][33] float2 (aT, q)
+  float* s_acc = s_dyn;                                             // [8 warps][CAP queue positions of a round][AS]
+  float* s_stage = s_dyn + 8 * CAP * AS;                            // [8 warps][G][33] float2 (aT, q)
   float4* s_pix = reinterpret_cast<float4*>(s_stage + 8 * G * BWD2_STRIDE * 2);  // [8 warps][34] {dLp r, g, b, -}
 
   const int tiles = p.tiles_x * p.tiles_y;
@@ -510,7 +514,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
   const float bx0 = (float)wx0, by0 = (float)wy0;
   const float bx1 = (float)min(wx0 + 7, p.W - 1), by1 = (float)min(wy0 + 3, p.H - 1);
   const uint32_t rec_base = smem_addr(s_rec);
-  const uint32_t acc_base = smem_addr(s_acc) + (uint32_t)w * (BATCH * AS * 4);
+  const uint32_t acc_base = smem_addr(s_acc) + (uint32_t)w * (CAP * AS * 4);
   const uint32_t stage_base = smem_addr(s_stage) + (uint32_t)w * (G * BWD2_STRIDE * 8);
   const uint32_t stage_wr = stage_base + (uint32_t)lane * 8;  // + i * 33 * 8 for hit i of the group
   // pass-2 role of this lane: hit j of the group, pixel rows {2h, 2h+1} of the block
@@ -650,8 +654,10 @@ blend_bwd2_kernel(BlendBwdParams p) {
       qn += __popc(m);
     }
     __syncwarp();
-    for (uint32_t g0 = 0; g0 < qn; g0 += G) {
-      const uint32_t ng = min((uint32_t)G, qn - g0);
+    for (uint32_t r0 = 0;; r0 += CAP) {
+    const uint32_t rend = min(qn, r0 + (uint32_t)CAP);
+    for (uint32_t g0 = r0; g0 < rend; g0 += G) {
+      const uint32_t ng = min((uint32_t)G, rend - g0);
       // ---- pass 1: lanes = pixels, one hit per iteration ----
 #pragma unroll 2
       for (uint32_t i = 0; i < ng; i++) {
@@ -691,10 +697,16 @@ blend_bwd2_kernel(BlendBwdParams p) {
       //   sum q dx   = gx S0 - Sx                  sum q dx^2  = gx^2 S0 - 2 gx Sx + Sxx
       //   sum q dy   = gy S0 - Sy                  sum q dx dy = gx gy S0 - gx Sy - gy Sx + Sxy
       //                                            sum q dy^2  = gy^2 S0 - 2 gy Sy + Syy
-      // (S0 = sum q, Sx = sum q c, Sxx = sum q c^2, ...; with two rows r in {0, 1}: Sy = Syy = row-1 sum, Sxy = row-1 Sx).
+      // (S0 = sum q, Sx = sum q c, Sxx = sum q c^2, ...).  The moments are taken about the CENTRE of the half (c' = c - 3.5,
+      // r' = r - 0.5 = -+0.5, g' = g - (3.5, 0.5)): for a Gaussian inside or next to the block the expansion about the
+      // block corner cancels (gx^2 S0 - 2 gx Sx + Sxx with every term ~10x the result), about the centre Sx', Sy' are
+      // small.  (Checked against a build with direct per-pixel sums: the scale / rotation gradients moved by less than
+      // the reference's own run-to-run spread, tools/grad_noise_floor.py.)
+      // With two rows: Sy' = (row1 - row0)/2, Syy' = S0/4, Sxy' = (Sx'_row1 - Sx'_row0)/2.
       // Only the |.| sums of dL/dmean2D still need d per pixel.
       const float gx = a.x - bx0;
       const float gy = (a.y - by0) - (float)(2u * h);
+      const float gxc = gx - 3.5f, gyc = gy - 0.5f;
       float v0 = 0, v1 = 0, v2 = 0, b3 = 0, b4 = 0;
       float R0[2], R1[2], R2[2];
 #pragma unroll
@@ -711,20 +723,21 @@ blend_bwd2_kernel(BlendBwdParams p) {
           v1 = fmaf(st.x, dl.y, v1);
           v2 = fmaf(st.x, dl.z, v2);
           r0 += st.y;
-          if (c > 0) r1 = fmaf(st.y, (float)c, r1);
-          if (c > 0) r2 = fmaf(st.y, (float)(c * c), r2);
+          r1 = fmaf(st.y, (float)c - 3.5f, r1);
+          r2 = fmaf(st.y, ((float)c - 3.5f) * ((float)c - 3.5f), r2);
           b3 += fabsf(st.y * fmaf(-a.z, (float)c, ub));
           b4 += fabsf(st.y * fmaf(-a.w, (float)c, wb));
         }
         R0[r] = r0; R1[r] = r1; R2[r] = r2;
       }
-      const float S0 = R0[0] + R0[1], Sx = R1[0] + R1[1], Sxx = R2[0] + R2[1], Sy = R0[1], Sxy = R1[1];
+      const float S0 = R0[0] + R0[1], Sx = R1[0] + R1[1], Sxx = R2[0] + R2[1];
+      const float Sy = 0.5f * (R0[1] - R0[0]), Sxy = 0.5f * (R1[1] - R1[0]);
       float v9 = S0;
-      float a3 = fmaf(gx, S0, -Sx);
-      float a4 = fmaf(gy, S0, -Sy);
-      float s6 = fmaf(gx, fmaf(gx, S0, -2.0f * Sx), Sxx);
-      float s7 = fmaf(gx, fmaf(gy, S0, -Sy), fmaf(-gy, Sx, Sxy));
-      float s8 = fmaf(gy, fmaf(gy, S0, -2.0f * Sy), Sy);
+      float a3 = fmaf(gxc, S0, -Sx);
+      float a4 = fmaf(gyc, S0, -Sy);
+      float s6 = fmaf(gxc, fmaf(gxc, S0, -2.0f * Sx), Sxx);
+      float s7 = fmaf(gxc, fmaf(gyc, S0, -Sy), fmaf(-gyc, Sx, Sxy));
+      float s8 = fmaf(gyc, fmaf(gyc, S0, -2.0f * Sy), 0.25f * S0);
       v0 += __shfl_xor_sync(0xffffffffu, v0, 16); v1 += __shfl_xor_sync(0xffffffffu, v1, 16);
       v2 += __shfl_xor_sync(0xffffffffu, v2, 16); v9 += __shfl_xor_sync(0xffffffffu, v9, 16);
       s6 += __shfl_xor_sync(0xffffffffu, s6, 16); s7 += __shfl_xor_sync(0xffffffffu, s7, 16);
@@ -736,15 +749,15 @@ blend_bwd2_kernel(BlendBwdParams p) {
         // dL/dconic = -0.5 G d d^T dL/dG;  |grad| accumulates the per-pixel absolute values
         const float o = bq.y;
         const float mo = -o, ho = -0.5f * o;
-        const uint32_t aa = acc_base + (g0 + j) * (uint32_t)(AS * 4);
+        const uint32_t aa = acc_base + (g0 - r0 + j) * (uint32_t)(AS * 4);
         sts128_at(aa, v0, v1, v2, mo * fmaf(a.z, a3, a.w * a4) * p.half_w);
         sts128_at(aa + 16, mo * fmaf(a.w, a3, bq.x * a4) * p.half_h, o * fmaf(p.half_w, b3, p.half_h * b4), ho * s6, ho * s7);
         sts64_at(aa + 32, ho * s8, v9);
       }
       __syncwarp();
     }
-    __syncthreads();
-    // ---- 3. one dense record per instance of this batch: sum (and clear) the 8 warps' accumulators ----
+    const int more = __syncthreads_or(qn > r0 + (uint32_t)CAP);
+    // ---- 3. one dense record per instance of this batch: sum the 8 warps' accumulator rows of this round ----
     // 16 bytes of a record per thread: three quarters come from the accumulators (values 0-9; words 10, 11 are pad
     // and stay zero), the fourth is zero so that every 32-byte sector is written whole
     for (uint32_t f = threadIdx.x; f < nb * 4; f += 256) {
@@ -755,13 +768,21 @@ blend_bwd2_kernel(BlendBwdParams p) {
 #pragma unroll
         for (int ww = 0; ww < 8; ww++) {   // warp order, as before: absent rows were zeros then and are skipped now
           const uint32_t qp = ((ww < 4 ? iv.x : iv.y) >> (8 * (ww & 3))) & 0xFFu;
-          if (qp != 0xFFu) {
-            const float4 x = reinterpret_cast<const float4*>(s_acc + ((size_t)ww * BATCH + qp) * AS)[q4];
+          if (qp - r0 < (uint32_t)CAP) {   // (0xFF and positions of other rounds fall outside)
+            const float4 x = reinterpret_cast<const float4*>(s_acc + ((size_t)ww * CAP + (qp - r0)) * AS)[q4];
             sum.x += x.x; sum.y += x.y; sum.z += x.z; sum.w += x.w;
           }
         }
       }
-      reinterpret_cast<float4*>(p.grec + (size_t)e_cur[sl] * NS)[q4] = sum;
+      float4* const rec = reinterpret_cast<float4*>(p.grec + (size_t)e_cur[sl] * NS) + q4;
+      if (r0 != 0) {   // a later round of an over-long queue: the same thread wrote this part in the round before
+        const float4 old = *rec;
+        sum.x += old.x; sum.y += old.y; sum.z += old.z; sum.w += old.w;
+      }
+      *rec = sum;
+    }
+    if (!more) break;
+    __syncthreads();   // the accumulator rows are free for the next round
     }
     // no barrier here: the next batch writes the OTHER halves of s_e / s_inv, and s_rec / s_acc only change hands at its barrier
     hi = lo;
@@ -779,13 +800,13 @@ static void launch_one(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
   blend_bwd_kernel<C, D, N, G, MINB><<<nblocks, 256, bytes, s>>>(p);
 }
 
-template <int BATCH, int MINB>
+template <int BATCH, int MINB, int CAP>
 static void launch_two_pass(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
   // dynamic shared memory: per-warp accumulators + per-warp (aT, q) staging tiles + per-warp pixel records
-  constexpr int bytes = 8 * BATCH * 12 * 4 + 8 * BWD2_GROUP * BWD2_STRIDE * 8 + 8 * 34 * 16;
-  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-  blend_bwd2_kernel<BATCH, MINB><<<nblocks, 256, bytes, s>>>(p);
+  constexpr int bytes = 8 * CAP * 12 * 4 + 8 * BWD2_GROUP * BWD2_STRIDE * 8 + 8 * 34 * 16;
+  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB, CAP>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  blend_bwd2_kernel<BATCH, MINB, CAP><<<nblocks, 256, bytes, s>>>(p);
 }
 
 void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s) {
@@ -799,9 +820,14 @@ void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bo
     static const int impl = [] { const char* e = getenv("IGS_BWD_IMPL"); return e ? atoi(e) : 2; }();
     static const int cfg = [] { const char* e = getenv("IGS_BWD2_CFG"); return e ? atoi(e) : 0; }();
     if (impl >= 2) {
-      if (cfg == 1) launch_two_pass<128, 2>(p, nblocks, s);
-      else if (cfg == 2) launch_two_pass<96, 2>(p, nblocks, s);
-      else launch_two_pass<64, 3>(p, nblocks, s);
+      // default: 128-instance batches with 48 accumulator rows per warp (3 CTAs/SM): half the block barriers of the
+      // 64-instance build and fuller pass-2 groups (C3: 9.40 -> 8.63 ms); IGS_BWD2_CFG selects the other builds
+      if (cfg == 1) launch_two_pass<64, 3, 64>(p, nblocks, s);
+      else if (cfg == 2) launch_two_pass<96, 3, 48>(p, nblocks, s);
+      else if (cfg == 3) launch_two_pass<96, 3, 64>(p, nblocks, s);
+      else if (cfg == 4) launch_two_pass<128, 2, 128>(p, nblocks, s);
+      else if (cfg == 5) launch_two_pass<128, 3, 32>(p, nblocks, s);
+      else launch_two_pass<128, 3, 48>(p, nblocks, s);
     } else if (occ >= 4) launch_one<false, false, false, false, 4>(p, nblocks, s);
     else launch_one<false, false, false, false, 3>(p, nblocks, s);
   } else if (coord && depth) launch_one<true, true, true, true, 2>(p, nblocks, s);

@@ -68,6 +68,7 @@ struct GatherBwdParams {
   int ns;  // floats per record (16 or 32)
   uint32_t capacity;  // emission slots the record buffer holds (R)
   float focal_x, focal_y, tan_fovx, tan_fovy, kernel_size;
+  int skip_geo;       // set by the launcher: 1 = colour-only records, the normal / plane block is skipped (preprocess_bwd.cu)
   const float* means3D;
   const Camera* cams;
   const float* cov3D;

@@ -16,6 +16,7 @@
 // (rasterizer_impl.cu:569), so computeCov2DCUDA's `combined_opacity` is dL_dconic[idx].w
 // (SURVEY T19).  IGS_STRICT_REF_BUGS (default 1) reproduces that; 0 uses the real opacity.
 #include "common.cuh"
+#include <cstdlib>
 #include "kernels.cuh"
 #include "mat3.cuh"
 
@@ -64,12 +65,14 @@ sum_records_kernel(size_t VP, const uint32_t* __restrict__ inst_off, const float
 #ifndef IGS_GATHER_MINB
 #define IGS_GATHER_MINB 4
 #endif
-// GEO = false is the colour-only build (16-float records, the refine loop): the cotangents of the normal / plane /
-// ray-point / depth outputs are identically zero there, every term they multiply is skipped, and the eigen data those
-// terms need (the largest gather of the kernel) is not loaded.  The full build computes the same values with the zeros
-// carried through (x + 0 * y == x for finite y), so the two agree wherever the reference's result is finite.
-template <bool GEO>
-__global__ void __launch_bounds__(128, GEO ? IGS_GATHER_MINB : 6)
+// Colour-only records (16 floats, the refine loop): the cotangents of the normal / plane / ray-point / depth outputs are
+// identically zero, so the block that turns them into dL/dVrk, dL/dnJ, dL/du,v,l — and the eigen-data gather it needs,
+// the largest of the kernel — is skipped AT RUN TIME (p.skip_geo; every value it would produce is an exact zero).
+// A separate colour-only BUILD with that block compiled out was 0.2 ms faster at C3 but is not used: with the block's
+// uses gone nvcc contracts the shared covariance chain differently, and on a few large, strongly anisotropic Gaussians
+// — where dL/dcov3D is a small residual of large terms — the scale / rotation gradients moved by 1e-3 relative, five
+// times further from the reference than this build, whose expressions mirror the reference's (tools/grad_noise_floor.py).
+__global__ void __launch_bounds__(128, IGS_GATHER_MINB)
 gather_bwd_kernel(GatherBwdParams p) {
   // Threads are indexed by DEPTH-SORTED position: emission slots of neighbouring positions are adjacent in grec, so
   // the record reads of a warp fall into one contiguous region (the small per-Gaussian inputs become the gathers).
@@ -90,7 +93,7 @@ gather_bwd_kernel(GatherBwdParams p) {
   float s[25];
 #pragma unroll
   for (int i = 0; i < 25; i++) s[i] = 0.0f;
-  if constexpr (!GEO) {
+  if (p.ns == 16) {
     const float4* r = reinterpret_cast<const float4*>(p.sums) + pos * 3;
     const float4 a = r[0], b = r[1], c = r[2];
     s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w; s[8] = c.x; s[9] = c.y;
@@ -112,7 +115,7 @@ gather_bwd_kernel(GatherBwdParams p) {
   {
     float nz = 0.0f;
 #pragma unroll
-    for (int i = 0; i < (GEO ? 25 : 10); i++) nz += fabsf(s[i]);
+    for (int i = 0; i < 25; i++) nz += fabsf(s[i]);
     if (nz == 0.0f) {
       part[0] = part[1] = part[2] = part[3] = make_float4(0, 0, 0, 0);
       return;
@@ -165,7 +168,7 @@ gather_bwd_kernel(GatherBwdParams p) {
   M3 dL_dVrk = m3_zero(), dL_dnJ = m3_zero();
   V3 plane = v3(0, 0, 0);
   float dL_du = 0, dL_dv = 0, dL_dl = 0, l = 1, nl = 1;
-  if constexpr (GEO) {
+  if (!p.skip_geo) {
   const GaussEig E = p.eig[g];
   M3 Vrk_inv, evecs;
 #pragma unroll
@@ -250,7 +253,7 @@ gather_bwd_kernel(GatherBwdParams p) {
     dL_dv = dL_dnl * 2 * tytz + dL_duvh.y + (dL_dnJ_inv.c[0][1] + dL_dnJ_inv.c[1][0]) * (-txtz) +
             2 * dL_dnJ_inv.c[0][0] * tytz - dL_dnJ_inv.c[2][1] + (cp0x * (-2 * t.y) + cp0y * t.x + cp1x * t.x) / nl;
   }
-  }  // GEO
+  }  // !skip_geo
 
   // ---- low-pass coefficient (double arithmetic where the reference has it) ----
   const float opacity = (float)((double)combined_opacity / ((double)coef + 1e-6));
@@ -290,14 +293,12 @@ gather_bwd_kernel(GatherBwdParams p) {
 #pragma unroll
     for (int i = 0; i < 6; i++) dcov[i] = 0;
   }
-  if constexpr (GEO) {
-    dcov[0] += dL_dVrk.c[0][0];
-    dcov[3] += dL_dVrk.c[1][1];
-    dcov[5] += dL_dVrk.c[2][2];
-    dcov[1] += dL_dVrk.c[0][1] + dL_dVrk.c[1][0];
-    dcov[2] += dL_dVrk.c[0][2] + dL_dVrk.c[2][0];
-    dcov[4] += dL_dVrk.c[1][2] + dL_dVrk.c[2][1];
-  }
+  dcov[0] += dL_dVrk.c[0][0];
+  dcov[3] += dL_dVrk.c[1][1];
+  dcov[5] += dL_dVrk.c[2][2];
+  dcov[1] += dL_dVrk.c[0][1] + dL_dVrk.c[1][0];
+  dcov[2] += dL_dVrk.c[0][2] + dL_dVrk.c[2][0];
+  dcov[4] += dL_dVrk.c[1][2] + dL_dVrk.c[2][1];
 
   const float dL_dT00 = 2 * (T.c[0][0] * Vrk.c[0][0] + T.c[0][1] * Vrk.c[0][1] + T.c[0][2] * Vrk.c[0][2]) * dL_da +
                         (T.c[1][0] * Vrk.c[0][0] + T.c[1][1] * Vrk.c[0][1] + T.c[1][2] * Vrk.c[0][2]) * dL_db;
@@ -318,29 +319,22 @@ gather_bwd_kernel(GatherBwdParams p) {
   const float dL_dJ12 = Wm.c[2][0] * dL_dT10 + Wm.c[2][1] * dL_dT11 + Wm.c[2][2] * dL_dT12;
 
   const float tz = 1.f / t.z, tz2 = tz * tz, tz3 = tz2 * tz;
-  float dL_dtx, dL_dty, dL_dtz;
-  if constexpr (!GEO) {
-    dL_dtx = x_grad_mul * (-h_x * tz2 * dL_dJ02);
-    dL_dty = y_grad_mul * (-h_y * tz2 * dL_dJ12);
-    dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 + (2 * h_y * t.y) * tz3 * dL_dJ12;
-  } else {
   const float l3 = l * l * l;
-  dL_dtx = x_grad_mul * (-h_x * tz2 * dL_dJ02 + dL_du * tz - dL_dnJ.c[0][2] * tz2 +
+  const float dL_dtx = x_grad_mul * (-h_x * tz2 * dL_dJ02 + dL_du * tz - dL_dnJ.c[0][2] * tz2 +
                                      dL_dnJ.c[2][0] * (1 / l - t.x * t.x / l3) + dL_dnJ.c[2][1] * (-t.x * t.y / l3) +
                                      dL_dnJ.c[2][2] * (-t.x * t.z / l3) + (cp0x * plane.x + cp0y * plane.y + cp2x) / nl +
                                      dL_dl * t.x / l);
-  dL_dty = y_grad_mul * (-h_y * tz2 * dL_dJ12 + dL_dv * tz - dL_dnJ.c[1][2] * tz2 +
+  const float dL_dty = y_grad_mul * (-h_y * tz2 * dL_dJ12 + dL_dv * tz - dL_dnJ.c[1][2] * tz2 +
                                      dL_dnJ.c[2][0] * (-t.x * t.y / l3) + dL_dnJ.c[2][1] * (1 / l - t.y * t.y / l3) +
                                      dL_dnJ.c[2][2] * (-t.y * t.z / l3) + (cp1x * plane.x + cp1y * plane.y + cp2y) / nl +
                                      dL_dl * t.y / l);
-  dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
+  const float dL_dtz = -h_x * tz2 * dL_dJ00 - h_y * tz2 * dL_dJ11 + (2 * h_x * t.x) * tz3 * dL_dJ02 +
                        (2 * h_y * t.y) * tz3 * dL_dJ12 - (dL_du * t.x + dL_dv * t.y) * tz2 +
                        (dL_dnJ.c[0][0] + dL_dnJ.c[1][1]) * (-tz2) + dL_dnJ.c[0][2] * (2 * t.x * tz3) +
                        dL_dnJ.c[1][2] * (2 * t.y * tz3) + (dL_dnJ.c[2][0] * t.x + dL_dnJ.c[2][1] * t.y) * (-t.z / l3) +
                        dL_dnJ.c[2][2] * (1 / l - t.z * t.z / l3) +
                        (cp0x * (-(v2 + 1)) + cp0y * uv + cp1x * uv + cp1y * (-(u2 + 1)) + cp2x * plane.x + cp2y * plane.y) / nl +
                        dL_dl * t.z / l;
-  }
 
   // dL_dmean from the covariance path: view^T (3x3) applied (transformVec4x3Transpose)
   V3 dmean = v3(view[0] * dL_dtx + view[1] * dL_dty + view[2] * dL_dtz,
@@ -360,7 +354,7 @@ gather_bwd_kernel(GatherBwdParams p) {
     d1.y = (proj[4] * m_w - proj[7] * mul1) * gx + (proj[5] * m_w - proj[7] * mul2) * gy;
     d1.z = (proj[8] * m_w - proj[11] * mul1) * gx + (proj[9] * m_w - proj[11] * mul2) * gy;
     V3 d2 = v3(0, 0, 0);
-    if constexpr (GEO) {
+    if (!p.skip_geo) {
       const V3 mv = v3(view[0] * m.x + view[4] * m.y + view[8] * m.z + view[12],
                        view[1] * m.x + view[5] * m.y + view[9] * m.z + view[13],
                        view[2] * m.x + view[6] * m.y + view[10] * m.z + view[14]);
@@ -584,8 +578,9 @@ void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s) {
   count_launch(2);
   if (p.ns == 16) sum_records_kernel<16><<<(unsigned)((VP * 4 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums, p.capacity);
   else sum_records_kernel<32><<<(unsigned)((VP * 8 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums, p.capacity);
-  if (p.ns == 16) gather_bwd_kernel<false><<<(unsigned)((VP + 127) / 128), 128, 0, s>>>(p);
-  else gather_bwd_kernel<true><<<(unsigned)((VP + 127) / 128), 128, 0, s>>>(p);
+  GatherBwdParams q = p;
+  q.skip_geo = p.ns == 16 ? 1 : 0;   // colour-only records: every geometry cotangent is zero
+  gather_bwd_kernel<<<(unsigned)((VP + 127) / 128), 128, 0, s>>>(q);
 }
 
 void launch_finish_bwd(const FinishBwdParams& p, cudaStream_t s) {

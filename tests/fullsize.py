@@ -42,13 +42,25 @@ GRAD_NAMES = ["means3D", "means2D", "sh", "opacities", "scales", "rotations"]
 N_PROBE = 1024
 
 
+def _activated_reproducible(sc):
+    """scenes.activated (exp, normalize, sigmoid) evaluated in float64 and rounded ONCE to float32.  torch's float32 CPU
+    exp runs vectorised per thread chunk and was seen to differ in the last bit between processes (5 of 45 runs at
+    P = 300k: tools/determinism_probe.sh), which moved the radii of ~10 Gaussians and with them every committed digest; the
+    float64 value rounds to the same float32 whatever code path computed it."""
+    scales = torch.from_numpy(np.exp(sc.log_scale.double().numpy()).astype(np.float32))
+    opac = torch.from_numpy((1.0 / (1.0 + np.exp(-sc.opacity_logit.double().numpy()))).astype(np.float32))
+    r = sc.rot.double()
+    rot = (r / r.norm(dim=1, keepdim=True).clamp_min(1e-12)).float()
+    return scales, rot, opac
+
+
 def inputs(name: str, dev):
     c = CASES[name]
     cfg = scenes.CONFIGS[c["cfg"]]
     P, W, H = cfg["P"], cfg["W"], cfg["H"]
     sc = scenes.make_gaussians(P, 0, cfg["log_scale_mean"])
     cams = scenes.make_cameras(cfg["V"], W, H, 1)
-    scales, rot, opac = scenes.activated(sc)
+    scales, rot, opac = _activated_reproducible(sc)
     vs = c["views"]
     g = torch.Generator().manual_seed(3 + 17 * len(vs))
     cot = torch.randn(len(vs), 3, H, W, generator=g)

@@ -73,7 +73,11 @@ def test_live_against_reference_build(ours):
     if ref is None:
         pytest.skip("baseline/_ref (reference CUDA build) did not travel to this box; digests / probes were asserted instead")
     name, inp, out = ours
-    r = fullsize.run_ref(ref, inp)
+    # The reference accumulates gradients with atomics: on the rotation gradient two single runs of the UNMODIFIED
+    # reference differ by up to 1.1e-3 max-normalised at C3 and two 3-run means still by 3e-4 (tools/grad_noise_floor.py,
+    # profiles/r02_grad_noise_floor.log), which made the 1e-3 bar a matter of luck with a 3-run mean.  The reference
+    # value is therefore the mean of 12 runs (a better estimate of the same quantity; the bar itself is unchanged).
+    r = fullsize.run_ref(ref, inp, grad_runs=12)
     assert out["R"] == r["R"]
     for n in fullsize.INT_NAMES:
         for v, (a, b) in enumerate(zip(out["ints"][n], r["ints"][n])):
@@ -87,5 +91,6 @@ def test_live_against_reference_build(ours):
         assert bool(torch.isfinite(a).all()), (name, n)
         e_max = float((a - b).abs().max() / (b.abs().max() + 1e-30))
         e_l2 = float((a - b).norm() / (b.norm() + 1e-30))
+        print(f"[{name}] grad {n:10s} max-norm {e_max:.3e} rel-l2 {e_l2:.3e}")
         assert e_max <= GRAD_RTOL, (name, n, e_max)
         assert e_l2 <= GRAD_RL2, (name, n, e_l2)
