@@ -477,7 +477,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
   constexpr int G = BWD2_GROUP;
   static_assert(BATCH <= 255 && BATCH % 32 == 0, "hit queue entries are bytes; whole 32-entry segments");
   static_assert(CAP % BWD2_GROUP == 0 && CAP <= BATCH, "groups do not straddle rounds");
-  __shared__ float4 s_rec[BATCH * 3];     // survivors: {x, y, conic.x, conic.y} {conic.z, opacity, r, g} {blue, tau, position, slot}
+  __shared__ float4 s_rec[BATCH * 3];     // survivors: {x, y, conic.x, conic.y} {conic.z, opacity, r, g} {blue, position, tau, slot}
   __shared__ float4 s_rawh[BATCH * 2];    // cp.async landing zone of the NEXT batch: heads as fetched (entry t: thread t's)
   __shared__ float s_rawb[BATCH];         //   blue
   __shared__ uint32_t s_rawe[BATCH];      //   emission slot
@@ -622,7 +622,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
       const uint32_t k = (uint32_t)w * 32u + __popc(bal & ((1u << lane) - 1u));
       s_rec[k] = ha;
       s_rec[BATCH + k] = hb;
-      s_rec[2 * BATCH + k] = make_float4(blue, tau, __uint_as_float(hi - threadIdx.x - range.x), __uint_as_float(threadIdx.x));
+      s_rec[2 * BATCH + k] = make_float4(blue, __uint_as_float(hi - threadIdx.x - range.x), tau, __uint_as_float(threadIdx.x));
     }
     // next batch: global -> shared copies now, its successor's list entries into a register
     if (lo > range.x) {
@@ -643,7 +643,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
         const float4 b = lds128<BATCH * 16>(ak);
         const float4 c = lds128<BATCH * 32>(ak);
         slot_of_k = __float_as_uint(c.w);
-        hit = (__float_as_uint(c.z) <= wlast) && block_can_contribute(a.x, a.y, a.z, a.w, b.x, c.y, bx0, by0, bx1, by1);
+        hit = (__float_as_uint(c.y) <= wlast) && block_can_contribute(a.x, a.y, a.z, a.w, b.x, c.z, bx0, by0, bx1, by1);
       }
       const uint32_t m = __ballot_sync(0xffffffffu, hit);
       if (hit) {
@@ -665,8 +665,8 @@ blend_bwd2_kernel(BlendBwdParams p) {
         const uint32_t ak = rec_base + kk * 16;
         const float4 a = lds128<0>(ak);
         const float4 bq = lds128<BATCH * 16>(ak);
-        const float4 cq = lds128<BATCH * 32>(ak);  // {blue, tau, position, slot}
-        const uint32_t pos = __float_as_uint(cq.z);
+        const float2 cq = lds64_at(ak + BATCH * 32);  // {blue, position}: one 8-byte load
+        const uint32_t pos = __float_as_uint(cq.y);
         float dx, dy;
         unpack2(sub2(pack2(a.x, a.y), pix2), dx, dy);  // each rounded like fsub()
         const float power = splat_power(dx, dy, a.z, a.w, bq.x);
