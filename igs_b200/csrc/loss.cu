@@ -142,20 +142,22 @@ __device__ __forceinline__ void stage_pairs(float2 (*dst)[LOSS_TCP], const float
 // VEC: asynchronous 16-byte global -> shared copies (cp.async, zero-filled outside the image): nothing passes through
 // registers and all of a thread's six copies are in flight at once (ncu r02: the register-staged loop made this kernel
 // latency bound — long-scoreboard 14.5 stalled warps per issue, 40 % issue utilisation).
+// Partials exist for the rows [r0, r1) this call owns only (pass 1 writes nothing else): every other row is staged as
+// zeros without being read, so the scratch needs no zero-fill in band mode.
 template <bool VEC>
 __device__ __forceinline__ void stage_partials(float2 (*dp)[LOSS_TCP], float (*ds)[LOSS_TC], const float2* __restrict__ D,
-                                               const float* __restrict__ E, int x0, int y0, int W, int H, int tid) {
+                                               const float* __restrict__ E, int x0, int y0, int W, int r0, int r1, int tid) {
   if constexpr (VEC) {
     for (int t = tid; t < LOSS_TH * (LOSS_TC / 2); t += 256) {   // 16 bytes = 2 pairs
       const int ty = t / (LOSS_TC / 2), g = t - ty * (LOSS_TC / 2);
       const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + 2 * g;
-      const bool ok = gy >= 0 && gy < H && gx >= 0 && gx < W;
+      const bool ok = gy >= r0 && gy < r1 && gx >= 0 && gx < W;
       cp_async16_zfill(smem_addr(&dp[ty][2 * g]), D + (ok ? (uint32_t)gy * (uint32_t)W + (uint32_t)gx : 0u), ok);
     }
     for (int t = tid; t < LOSS_TH * (LOSS_TC / 4); t += 256) {   // 16 bytes = 4 scalars
       const int ty = t / (LOSS_TC / 4), g = t - ty * (LOSS_TC / 4);
       const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + 4 * g;
-      const bool ok = gy >= 0 && gy < H && gx >= 0 && gx < W;
+      const bool ok = gy >= r0 && gy < r1 && gx >= 0 && gx < W;
       cp_async16_zfill(smem_addr(&ds[ty][4 * g]), E + (ok ? (uint32_t)gy * (uint32_t)W + (uint32_t)gx : 0u), ok);
     }
     cp_async_commit();
@@ -163,7 +165,7 @@ __device__ __forceinline__ void stage_partials(float2 (*dp)[LOSS_TCP], float (*d
     for (int t = tid; t < LOSS_TH * LOSS_TC; t += 256) {
       const int ty = t / LOSS_TC, tx = t - ty * LOSS_TC;
       const int gy = y0 + ty - LOSS_R, gx = x0 - LOSS_X0 + tx;
-      const bool ok = gy >= 0 && gy < H && gx >= 0 && gx < W;
+      const bool ok = gy >= r0 && gy < r1 && gx >= 0 && gx < W;
       const uint32_t o = ok ? (uint32_t)gy * (uint32_t)W + (uint32_t)gx : 0u;
       dp[ty][tx] = ok ? D[o] : make_float2(0.0f, 0.0f);
       ds[ty][tx] = ok ? E[o] : 0.0f;
@@ -185,7 +187,7 @@ loss_pass1_kernel(LossParams p) {
   const int tid = threadIdx.x;
   int r0, r1;
   loss_row_range(p, plane, r0, r1);
-  if (y0 >= r1 || y0 + LOSS_BY <= r0) {  // no owned row in this tile (scratch and dpred were zero-filled by the launcher)
+  if (y0 >= r1 || y0 + LOSS_BY <= r0) {  // no owned row in this tile: nothing to write (pass 2 reads owned rows only)
     if (tid == 0) p.partial[((size_t)blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x] = 0.0;
     return;
   }
@@ -319,8 +321,17 @@ loss_pass2_kernel(LossParams p) {
   const int tid = threadIdx.x;
   int r0, r1;
   loss_row_range(p, plane, r0, r1);
-  if (y0 >= r1 + LOSS_R || y0 + LOSS_BY <= r0 - LOSS_R) return;  // dL/dpred is zero here (pre-filled by the launcher)
-  stage_partials<VEC>(s01, s2, p.d01 + po, p.dE12 + po, x0, y0, p.W, p.H, tid);
+  if (y0 >= r1 + LOSS_R || y0 + LOSS_BY <= r0 - LOSS_R) {  // out of reach of every owned row: dL/dpred is zero here
+    const int c = tid % LOSS_BX, rg = tid / LOSS_BX;
+    float* __restrict__ O = p.dpred + po;
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      const int gx = x0 + c, gy = y0 + rg * 4 + j;
+      if (gx < p.W && gy < p.H) O[(uint32_t)gy * (uint32_t)p.W + (uint32_t)gx] = 0.0f;
+    }
+    return;
+  }
+  stage_partials<VEC>(s01, s2, p.d01 + po, p.dE12 + po, x0, y0, p.W, r0, r1, tid);
   if constexpr (VEC) cp_async_wait_all();
   __syncthreads();
   f32x2 w2[11];
@@ -481,9 +492,7 @@ void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W,
                                      reinterpret_cast<uintptr_t>(p.d01)) % 16 == 0) && ((size_t)H * W < (1ull << 31));
   const dim3 grid_all((W + LOSS_BX - 1) / LOSS_BX, (H + LOSS_BY - 1) / LOSS_BY, V * 3);
   const size_t nblk = (size_t)grid_all.x * grid_all.y * grid_all.z;
-  if (p.has_rows) cudaMemsetAsync(dpred, 0, (size_t)V * 3 * N * sizeof(float), s);   // rows nobody here owns
   if (!by_view) {
-    if (p.has_rows) cudaMemsetAsync(p.d01, 0, 3 * planes * N * sizeof(float), s);     // (pass 2 reads a 5-row halo of them)
     count_launch(2);
     if (vec) {
       loss_pass1_kernel<true><<<grid_all, 256, 0, s>>>(p);
@@ -500,10 +509,7 @@ void launch_refine_loss(const float* pred, const float* gt, int V, int H, int W,
       q.planes = 3;
       q.pred = pred + (size_t)v * 3 * N; q.gt = gt + (size_t)v * 3 * N; q.dpred = dpred + (size_t)v * 3 * N;
       q.partial = p.partial + (size_t)v * nblk_view;
-      if (p.has_rows) {
-        q.rows[0] = p.rows[2 * v]; q.rows[1] = p.rows[2 * v + 1];
-        cudaMemsetAsync(q.d01, 0, 9 * N * sizeof(float), s);    // the previous view's partials, outside this view's rows
-      }
+      if (p.has_rows) { q.rows[0] = p.rows[2 * v]; q.rows[1] = p.rows[2 * v + 1]; }
       count_launch(2);
       if (vec) {
         loss_pass1_kernel<true><<<grid, 256, 0, s>>>(q);
