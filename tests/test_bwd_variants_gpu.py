@@ -1,0 +1,56 @@
+"""GPU: the batch / accumulator-row builds of the colour-only backward (IGS_BWD2_CFG) and the
+first-generation kernel (IGS_BWD_IMPL=1) compute the same gradients as the default build on a full-size case.  The
+variants differ only in how a tile's instance list is cut into batches and rounds, i.e. in the order of a few additions:
+the bar is 1e-4 max-normalised (ten times tighter than the bar against the reference).  Build 5 (128-instance batches,
+32 accumulator rows per warp) takes the multi-round write-out path on most dense tiles.
+
+The switches are read once per process, so every variant runs in its own interpreter (tools/grad_noise_floor.py)."""
+import os
+import subprocess
+import sys
+from pathlib import Path
+
+import pytest
+
+torch = pytest.importorskip("torch")
+pytestmark = pytest.mark.gpu
+
+ROOT = Path(__file__).resolve().parent.parent
+
+
+def _run(env_extra, out):
+    env = dict(os.environ)
+    for k in ("IGS_BWD2_CFG", "IGS_BWD_IMPL"):
+        env.pop(k, None)
+    env.update(env_extra)
+    r = subprocess.run([sys.executable, str(ROOT / "tools" / "grad_noise_floor.py"), "--case", "C2", "--no-ref", "--save", str(out)],
+                       env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    return torch.load(out)
+
+
+@pytest.fixture(scope="module")
+def base(tmp_path_factory):
+    if not torch.cuda.is_available():
+        pytest.skip("no CUDA device")
+    return _run({}, tmp_path_factory.mktemp("bwd_variants") / "base.pt")
+
+
+# (variant, bar): the batch builds only reorder additions; the first-generation kernel is a different formulation of the
+# same sums (per-pair reduction instead of per-pixel (aT, q) staging) and gets the bar used against the reference
+@pytest.mark.parametrize("variant,bar", [({"IGS_BWD2_CFG": "1"}, 1e-4), ({"IGS_BWD2_CFG": "5"}, 1e-4), ({"IGS_BWD_IMPL": "1"}, 1e-3)],
+                         ids=["batch64_rows64", "batch128_rows32", "first_generation"])
+def test_backward_variants_agree_with_the_default_build(cuda_dev, base, tmp_path, variant, bar):
+    sys.path.insert(0, str(ROOT / "tests"))
+    import fullsize
+    import numpy as np
+    rm = fullsize.rotation_mask(fullsize.inputs("C2", torch.device("cpu")))
+    other = _run(variant, tmp_path / "variant.pt")
+    for n, b in base.items():
+        a, b = other[n].double(), b.double()
+        assert bool(torch.isfinite(a).all()), n
+        if n == "rotations" and not isinstance(rm, slice):
+            keep = torch.from_numpy(np.asarray(rm))
+            a, b = a[keep], b[keep]
+        e = float((a - b).abs().max() / (b.abs().max() + 1e-30))
+        assert e <= bar, (variant, n, e)
