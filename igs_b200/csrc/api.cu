@@ -320,6 +320,7 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   // remember which ping-pong buffer holds the sorted instances (bit 16 of flags)
   {
     hv.flags |= ((uint32_t)bcur << 16);
+    if (R > 0 && blend_fwd_writes_hitmask()) hv.flags |= (1u << 17);   // block-hit bytes in the other tile-key buffer
     count_launch();
     write_header_kernel<<<1, 1, 0, s>>>(G.hdr, hv, d_total, capmode ? R : 0u, a->status);
     hv.R = R;
@@ -330,6 +331,10 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
 
   BlendFwdParams bp;
   bp.counters = nullptr;
+  // Block-hit bytes for the backward pass live in the tile-key buffer the sort did not finish in (dead after the sort);
+  // instances the forward never stages (behind the point where a tile's pixels are all opaque) keep the zero.
+  bp.hitmask = (hv.flags & (1u << 17)) ? reinterpret_cast<uint8_t*>(B.tkey[bcur ^ 1]) : nullptr;
+  if (bp.hitmask) IGS_CUDA_CHECK(cudaMemsetAsync(bp.hitmask, 0, R, s));
   bp.W = W; bp.H = H; bp.tiles_x = tiles_x; bp.tiles_y = tiles_y; bp.focal_x = focal_x; bp.focal_y = focal_y;
   bp.ranges = I.ranges; bp.point_list = B.point_list; bp.head = G.head; bp.tail = G.tail; bp.bg = a->background;
   bp.out_color = a->out_color; bp.out_coord = a->out_coord; bp.out_mcoord = a->out_mcoord; bp.out_depth = a->out_depth;
@@ -416,6 +421,7 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
     bp.dL_color = a->dL_dout_color; bp.dL_coord = a->dL_dout_coord; bp.dL_mcoord = a->dL_dout_mcoord;
     bp.dL_depth = a->dL_dout_depth; bp.dL_mdepth = a->dL_dout_mdepth; bp.dL_alpha = a->dL_dout_alpha;
     bp.dL_normal = a->dL_dout_normal; bp.grec = grec;
+    bp.hitmask = (hv.flags & (1u << 17)) ? reinterpret_cast<const uint8_t*>(B.tkey[bcur ^ 1]) : nullptr;
     { StageScope st(IGS_STAGE_BLEND_BWD, s); launch_blend_bwd(bp, V, coord, depth, geograd, s); }
     if (int e = debug_sync(dbg, s, "blend backward")) return e;
   }

@@ -469,7 +469,12 @@ __device__ __forceinline__ void sts128_at(uint32_t addr, float a, float b, float
 // CAP = accumulator rows per warp (a multiple of the group size).  A warp whose queue for one batch is longer than CAP
 // works it off in rounds of CAP hits with a write-out after each (later rounds add to the record in global memory);
 // with CAP = BATCH there is exactly one round.  A smaller CAP buys a larger BATCH at the same shared-memory footprint.
-template <int BATCH, int MINB, int CAP>
+// MASK: the forward pass left one byte per instance with the blocks of its tile it can reach (BlendBwdParams::hitmask).
+// Then neither the tile-level cull (alpha extent against the tile) nor the eight per-block tests are repeated here: an
+// instance survives when its byte is non-zero and warp w queues it when bit w is set — the same pairs the tests below
+// select (the forward evaluates them for every instance at or before a block's last contributor), at a fraction of the
+// instructions (the per-warp cull was 11.5 % of this kernel's).  MASK = false keeps the self-contained cull.
+template <int BATCH, int MINB, int CAP, bool MASK>
 __global__ void __launch_bounds__(256, MINB)
 blend_bwd2_kernel(BlendBwdParams p) {
   constexpr int NS = 16;  // floats per gradient record in global memory
@@ -477,7 +482,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
   constexpr int G = BWD2_GROUP;
   static_assert(BATCH <= 255 && BATCH % 32 == 0, "hit queue entries are bytes; whole 32-entry segments");
   static_assert(CAP % BWD2_GROUP == 0 && CAP <= BATCH, "groups do not straddle rounds");
-  __shared__ float4 s_rec[BATCH * 3];     // survivors: {x, y, conic.x, conic.y} {conic.z, opacity, r, g} {blue, position, tau, slot}
+  __shared__ float4 s_rec[BATCH * 3];     // survivors: {x, y, conic.x, conic.y} {conic.z, opacity, r, g} {blue, position, tau | hit byte, slot}
   __shared__ float4 s_rawh[BATCH * 2];    // cp.async landing zone of the NEXT batch: heads as fetched (entry t: thread t's)
   __shared__ float s_rawb[BATCH];         //   blue
   __shared__ uint32_t s_rawe[BATCH];      //   emission slot
@@ -578,10 +583,18 @@ blend_bwd2_kernel(BlendBwdParams p) {
     const uint32_t lo_b = (hi_b - range.x > BATCH) ? hi_b - BATCH : range.x;
     return (threadIdx.x < hi_b - lo_b) ? p.point_list[hi_b - 1 - threadIdx.x] : 0u;
   };
-  uint32_t gid_next = 0;
+  auto load_mask = [&](uint32_t hi_b) -> uint32_t {  // its block-hit byte (MASK)
+    if (!MASK || hi_b <= range.x) return 0u;
+    const uint32_t lo_b = (hi_b - range.x > BATCH) ? hi_b - BATCH : range.x;
+    return (threadIdx.x < hi_b - lo_b) ? (uint32_t)p.hitmask[hi_b - 1 - threadIdx.x] : 0u;
+  };
+  uint32_t gid_next = 0, mask_cur = 0, mask_next = 0;
   if (end > range.x) {
     issue_copies(end, load_gid(end));
-    gid_next = load_gid((end - range.x > BATCH) ? end - BATCH : range.x);
+    mask_cur = load_mask(end);
+    const uint32_t hi2 = (end - range.x > BATCH) ? end - BATCH : range.x;
+    gid_next = load_gid(hi2);
+    mask_next = load_mask(hi2);
   }
 
   // zero records of never-visited instances
@@ -613,8 +626,13 @@ blend_bwd2_kernel(BlendBwdParams p) {
       hb = lds128_at(rawh_addr + 16);
       blue = s_rawb[threadIdx.x];
       e_cur[threadIdx.x] = s_rawe[threadIdx.x];
-      keep = alpha_extent(ha.z, ha.w, hb.x, hb.y, ex, ey, tau);
-      keep = keep && (ha.x + ex >= tx0) && (ha.x - ex <= tx1) && (ha.y + ey >= ty0) && (ha.y - ey <= ty1);
+      if constexpr (MASK) {
+        keep = mask_cur != 0u;
+        tau = __uint_as_float(mask_cur);
+      } else {
+        keep = alpha_extent(ha.z, ha.w, hb.x, hb.y, ex, ey, tau);
+        keep = keep && (ha.x + ex >= tx0) && (ha.x - ex <= tx1) && (ha.y + ey >= ty0) && (ha.y - ey <= ty1);
+      }
     }
     const uint32_t bal = __ballot_sync(0xffffffffu, keep);
     if (lane == 0) s_wcount[w] = __popc(bal);
@@ -627,7 +645,10 @@ blend_bwd2_kernel(BlendBwdParams p) {
     // next batch: global -> shared copies now, its successor's list entries into a register
     if (lo > range.x) {
       issue_copies(lo, gid_next);
-      gid_next = load_gid((lo - range.x > BATCH) ? lo - BATCH : range.x);
+      mask_cur = mask_next;
+      const uint32_t hi2 = (lo - range.x > BATCH) ? lo - BATCH : range.x;
+      gid_next = load_gid(hi2);
+      mask_next = load_mask(hi2);
     }
     __syncthreads();
     // ---- 2. per-warp traversal ----
@@ -639,11 +660,15 @@ blend_bwd2_kernel(BlendBwdParams p) {
       uint32_t slot_of_k = 0;
       if ((uint32_t)lane < s_wcount[seg]) {
         const uint32_t ak = rec_base + k * 16;
-        const float4 a = lds128<0>(ak);
-        const float4 b = lds128<BATCH * 16>(ak);
         const float4 c = lds128<BATCH * 32>(ak);
         slot_of_k = __float_as_uint(c.w);
-        hit = (__float_as_uint(c.y) <= wlast) && block_can_contribute(a.x, a.y, a.z, a.w, b.x, c.z, bx0, by0, bx1, by1);
+        if constexpr (MASK) {
+          hit = (__float_as_uint(c.y) <= wlast) && ((__float_as_uint(c.z) >> w) & 1u);
+        } else {
+          const float4 a = lds128<0>(ak);
+          const float4 b = lds128<BATCH * 16>(ak);
+          hit = (__float_as_uint(c.y) <= wlast) && block_can_contribute(a.x, a.y, a.z, a.w, b.x, c.z, bx0, by0, bx1, by1);
+        }
       }
       const uint32_t m = __ballot_sync(0xffffffffu, hit);
       if (hit) {
@@ -800,13 +825,19 @@ static void launch_one(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
   blend_bwd_kernel<C, D, N, G, MINB><<<nblocks, 256, bytes, s>>>(p);
 }
 
-template <int BATCH, int MINB, int CAP>
-static void launch_two_pass(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
+template <int BATCH, int MINB, int CAP, bool MASK>
+static void launch_two_pass_m(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
   // dynamic shared memory: per-warp accumulators + per-warp (aT, q) staging tiles + per-warp pixel records
   constexpr int bytes = 8 * CAP * 12 * 4 + 8 * BWD2_GROUP * BWD2_STRIDE * 8 + 8 * 34 * 16;
-  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB, CAP>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
-  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB, CAP>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
-  blend_bwd2_kernel<BATCH, MINB, CAP><<<nblocks, 256, bytes, s>>>(p);
+  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB, CAP, MASK>, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+  cudaFuncSetAttribute(blend_bwd2_kernel<BATCH, MINB, CAP, MASK>, cudaFuncAttributePreferredSharedMemoryCarveout, 100);
+  blend_bwd2_kernel<BATCH, MINB, CAP, MASK><<<nblocks, 256, bytes, s>>>(p);
+}
+
+template <int BATCH, int MINB, int CAP>
+static void launch_two_pass(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
+  if (p.hitmask != nullptr) launch_two_pass_m<BATCH, MINB, CAP, true>(p, nblocks, s);
+  else launch_two_pass_m<BATCH, MINB, CAP, false>(p, nblocks, s);
 }
 
 void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s) {

@@ -37,6 +37,10 @@ blend_fwd_kernel(BlendFwdParams p) {
   __shared__ float4 s_t[GEO ? BLEND_BATCH * 4 : 1];  // tails of the survivors
   __shared__ uint32_t s_gid[BLEND_BATCH];
   __shared__ uint32_t s_wcount[8];
+  // Hit masks for the backward pass: s_ball[w][seg] = ballot of "survivor 32 seg + lane can reach warp w's 8x4 block".
+  // After a batch every survivor's eight bits are gathered into ONE byte per instance (p.hitmask, by list position), so the
+  // backward neither repeats the tile-level cull nor the eight per-block tests: it walks exactly these pairs.
+  __shared__ uint32_t s_ball[8][BLEND_BATCH / 32];
 
   const int tiles = p.tiles_x * p.tiles_y;
   const int gt = blockIdx.x;
@@ -76,8 +80,24 @@ blend_fwd_kernel(BlendFwdParams p) {
   float mCo0 = 0, mCo1 = 0, mCo2 = 0, mDepth = 0;
   const f32x2 pix2 = pack2(pixfx, pixfy);
 
+  // one byte per survivor of the batch just blended (all eight warps' ballots are complete after a block barrier)
+  uint32_t prev_count = 0;
+  auto write_hit_masks = [&]() {
+    if (threadIdx.x < prev_count) {
+      const uint32_t seg = threadIdx.x >> 5;
+      uint32_t mk = 0;
+#pragma unroll
+      for (int ww = 0; ww < 8; ww++) mk |= ((s_ball[ww][seg] >> lane) & 1u) << ww;
+      const uint32_t pos = __float_as_uint(s_rec[2 * BLEND_BATCH + threadIdx.x].z);   // 1-based list position
+      p.hitmask[range.x + pos - 1] = (uint8_t)mk;
+    }
+    prev_count = 0;
+  };
+  const bool masks = !COUNT && p.hitmask != nullptr;
   for (uint32_t start = range.x; start < range.y; start += BLEND_BATCH) {
-    if (__syncthreads_count(done != 0) == 256) break;
+    const int ndone = __syncthreads_count(done != 0);
+    if (masks && prev_count) write_hit_masks();
+    if (ndone == 256) break;
     // ---- 1. fetch + tile-level cull + ordered compaction ----
     uint32_t j = start + threadIdx.x;
     bool keep = false;
@@ -95,6 +115,8 @@ blend_fwd_kernel(BlendFwdParams p) {
     uint32_t bal = __ballot_sync(0xffffffffu, keep);
     if (lane == 0) s_wcount[w] = __popc(bal);
     __syncthreads();
+    // (every thread has finished gathering the previous batch's ballots; the next ballot is stored after another barrier)
+    if (masks && threadIdx.x < 8 * (BLEND_BATCH / 32)) (&s_ball[0][0])[threadIdx.x] = 0u;
     uint32_t woff = 0, count = 0;
 #pragma unroll
     for (int ww = 0; ww < 8; ww++) {
@@ -132,6 +154,7 @@ blend_fwd_kernel(BlendFwdParams p) {
           hit = block_can_contribute(a.x, a.y, a.z, a.w, b.x, tk, bx0, by0, bx1, by1);
         }
         uint32_t m = __ballot_sync(0xffffffffu, hit);
+        if (masks && lane == 0) s_ball[w][base >> 5] = m;
         while (m) {
           const uint32_t kk = base + (__ffs(m) - 1);
           m &= m - 1;
@@ -190,6 +213,11 @@ blend_fwd_kernel(BlendFwdParams p) {
         if (__all_sync(0xffffffffu, done != 0)) break;
       }
     }
+    prev_count = count;
+  }
+  if (masks && prev_count) {   // the list ended with the last batch: no loop-top barrier came after its blend
+    __syncthreads();
+    write_hit_masks();
   }
 
   if constexpr (COUNT) {
@@ -534,6 +562,15 @@ static void launch_fwd2_cfg(const BlendFwdParams& p, int nblocks, bool coord, bo
 static void launch_fwd2(const BlendFwdParams& p, int nblocks, bool coord, bool depth, bool occ4, bool big, cudaStream_t s) {
   if (occ4) { if (big) launch_fwd2_cfg<4, 256>(p, nblocks, coord, depth, s); else launch_fwd2_cfg<4, 128>(p, nblocks, coord, depth, s); }
   else { if (big) launch_fwd2_cfg<3, 256>(p, nblocks, coord, depth, s); else launch_fwd2_cfg<3, 128>(p, nblocks, coord, depth, s); }
+}
+
+bool blend_fwd_writes_hitmask() {
+  static const bool on = [] {
+    const char* e = getenv("IGS_HITMASK");
+    const char* i = getenv("IGS_FWD_IMPL");
+    return !(e && atoi(e) == 0) && !(i && atoi(i) >= 2);   // the cp.async experiment kernel does not write them
+  }();
+  return on;
 }
 
 void launch_blend_fwd(const BlendFwdParams& p, int V, bool coord, bool depth, cudaStream_t s) {

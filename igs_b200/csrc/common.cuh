@@ -52,7 +52,8 @@ struct Header {
   uint32_t P, V, N;       // N = W*H
   uint32_t R;             // total instances (filled after the scan)
   uint32_t tiles_x, tiles_y;
-  uint32_t flags;         // bit0 coord, bit1 depth, bit2 normal, bit3 has_scales, bit4 has_shs
+  uint32_t flags;         // bit0 coord, bit1 depth, bit2 normal, bit3 has_scales, bit4 has_shs, bit8 / bit16 which ping-pong
+                          // buffer the depth / tile sort finished in, bit17 block-hit bytes written by the forward blend
   uint32_t pad[8];
 };
 static_assert(sizeof(Header) == 64, "Header size");

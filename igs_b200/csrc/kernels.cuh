@@ -35,6 +35,7 @@ struct BlendFwdParams {
   float* accum_depth;
   float* normal_length;
   unsigned long long* counters;  // instrumentation build only (igs_count_blend_pairs)
+  uint8_t* hitmask;              // [R] by list position: bit w = the instance can reach block w of its tile (nullptr: not written)
 };
 
 struct BlendBwdParams {
@@ -61,6 +62,7 @@ struct BlendBwdParams {
   const float* dL_alpha;
   const float* dL_normal;
   float* grec;  // [R][NS]
+  const uint8_t* hitmask;  // [R] block-hit bytes written by the forward pass (nullptr: the backward culls by itself)
 };
 
 struct GatherBwdParams {
@@ -126,6 +128,7 @@ void launch_finalize_bins(uint32_t R, const uint32_t* n_dev, const uint32_t* tke
 void launch_decode_keys(uint32_t R, uint32_t tiles_per_view, uint32_t P, const uint32_t* tkey,
                         const uint32_t* point_list, const float* depth, uint64_t* keys, uint32_t* plist_local,
                         cudaStream_t s);
+bool blend_fwd_writes_hitmask();   // whether the forward kernel in use fills BlendFwdParams::hitmask (IGS_HITMASK=0: off)
 void launch_blend_fwd(const BlendFwdParams& p, int V, bool coord, bool depth, cudaStream_t s);
 void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s);
 void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s);
