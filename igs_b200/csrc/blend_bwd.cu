@@ -567,14 +567,16 @@ blend_bwd2_kernel(BlendBwdParams p) {
   //   * its head / blue / emission slot are copied global -> shared with cp.async ONE batch ahead,
   // both while the warps traverse the current batch; a batch therefore starts from data already in shared memory.
   // Every thread copies, waits for and reads only ITS OWN landing-zone entry, so no barrier is needed for it.
-  auto issue_copies = [&](uint32_t hi_b, uint32_t gid_b) {
+  auto issue_copies = [&](uint32_t hi_b, uint32_t gid_b, uint32_t mask_b) {
     const uint32_t lo_b = (hi_b - range.x > BATCH) ? hi_b - BATCH : range.x;
     if (threadIdx.x < hi_b - lo_b) {
-      const float4* hp = reinterpret_cast<const float4*>(p.head + gid_b);
-      cp_async16(rawh_addr, hp);
-      cp_async16(rawh_addr + 16, hp + 1);
-      cp_async4(rawb_addr, &p.tail[gid_b].a.x);
-      cp_async4(rawe_addr, p.point_e + (hi_b - 1 - threadIdx.x));
+      if (!MASK || mask_b != 0u) {   // (MASK: an instance that reaches no block is never looked at again)
+        const float4* hp = reinterpret_cast<const float4*>(p.head + gid_b);
+        cp_async16(rawh_addr, hp);
+        cp_async16(rawh_addr + 16, hp + 1);
+        cp_async4(rawb_addr, &p.tail[gid_b].a.x);
+      }
+      cp_async4(rawe_addr, p.point_e + (hi_b - 1 - threadIdx.x));   // every instance gets a record
     }
     cp_async_commit();
   };
@@ -590,8 +592,8 @@ blend_bwd2_kernel(BlendBwdParams p) {
   };
   uint32_t gid_next = 0, mask_cur = 0, mask_next = 0;
   if (end > range.x) {
-    issue_copies(end, load_gid(end));
     mask_cur = load_mask(end);
+    issue_copies(end, load_gid(end), mask_cur);
     const uint32_t hi2 = (end - range.x > BATCH) ? end - BATCH : range.x;
     gid_next = load_gid(hi2);
     mask_next = load_mask(hi2);
@@ -644,7 +646,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
     }
     // next batch: global -> shared copies now, its successor's list entries into a register
     if (lo > range.x) {
-      issue_copies(lo, gid_next);
+      issue_copies(lo, gid_next, mask_next);
       mask_cur = mask_next;
       const uint32_t hi2 = (lo - range.x > BATCH) ? lo - BATCH : range.x;
       gid_next = load_gid(hi2);
