@@ -333,8 +333,8 @@ int igs_rasterize_forward(const igs_forward_args* a, igs_alloc_fn geom_alloc, vo
   bp.counters = nullptr;
   // Block-hit bytes for the backward pass live in the tile-key buffer the sort did not finish in (dead after the sort);
   // instances the forward never stages (behind the point where a tile's pixels are all opaque) keep the zero.
-  bp.hitmask = (hv.flags & (1u << 17)) ? reinterpret_cast<uint8_t*>(B.tkey[bcur ^ 1]) : nullptr;
-  if (bp.hitmask) IGS_CUDA_CHECK(cudaMemsetAsync(bp.hitmask, 0, R, s));
+  bp.hitmask = reinterpret_cast<uint8_t*>(B.tkey[bcur ^ 1]);   // (R == 0: no tile has a list, nothing is written)
+  if (R > 0) IGS_CUDA_CHECK(cudaMemsetAsync(bp.hitmask, 0, R, s));
   bp.W = W; bp.H = H; bp.tiles_x = tiles_x; bp.tiles_y = tiles_y; bp.focal_x = focal_x; bp.focal_y = focal_y;
   bp.ranges = I.ranges; bp.point_list = B.point_list; bp.head = G.head; bp.tail = G.tail; bp.bg = a->background;
   bp.out_color = a->out_color; bp.out_coord = a->out_coord; bp.out_mcoord = a->out_mcoord; bp.out_depth = a->out_depth;
