@@ -77,7 +77,6 @@ blend_fwd_kernel(BlendFwdParams p) {
   f32x2 Co0D = pack2(0.0f, 0.0f), Co12 = pack2(0.0f, 0.0f);  // (Co0, Depth), (Co1, Co2)
   f32x2 N01 = pack2(0.0f, 0.0f);
   float N2 = 0;
-  float mCo0 = 0, mCo1 = 0, mCo2 = 0, mDepth = 0;
   const f32x2 pix2 = pack2(pixfx, pixfy);
 
   // one byte per survivor of the batch just blended (all eight warps' ballots are complete after a block barrier)
@@ -192,12 +191,8 @@ blend_fwd_kernel(BlendFwdParams p) {
               const float c1 = ffma(dy, t3.y, ffma(dx, t3.x, t2.x));
               const float c2 = ffma(dy, t3.w, ffma(dx, t3.z, t2.y));
               Co12 = fma2(aT2, pack2(c1, c2), Co12);
-              if (before_median) { mCo0 = c0; mCo1 = c1; mCo2 = c2; }
             }
-            if constexpr (DEPTH) {
-              tt = t0.y + (t0.z * dx + t0.w * dy);
-              if (before_median) mDepth = tt;
-            }
+            if constexpr (DEPTH) tt = fadd(t0.y, ffma(t0.z, dx, fmul(t0.w, dy)));
             if constexpr (COORD || DEPTH) Co0D = fma2(aT2, pack2(c0, tt), Co0D);
             if constexpr (NORMAL) {
               N01 = fma2(aT2, pack2(t1.x, t1.y), N01);
@@ -242,6 +237,29 @@ blend_fwd_kernel(BlendFwdParams p) {
   unpack2(Co0D, Co0, Depth);
   unpack2(Co12, Co1, Co2);
   unpack2(N01, N0, N1);
+  // Median coordinate / depth = the values of the LAST contributor blended while T > 0.5 (max_contributor).  Carrying them
+  // through the traversal cost four selects per (block, instance) hit; they are re-evaluated here, once per pixel, from
+  // that one instance's records with the same rounded operations as in the loop.
+  float mCo0 = 0, mCo1 = 0, mCo2 = 0, mDepth = 0;
+  if constexpr (GEO) {
+    if (inside && max_contributor != 0xFFFFFFFFu) {
+      const uint32_t gid = p.point_list[range.x + max_contributor - 1];
+      const float4 ha = p.head[gid].a;
+      const float4* tp = reinterpret_cast<const float4*>(p.tail + gid);
+      float dx, dy;
+      unpack2(sub2(pack2(ha.x, ha.y), pix2), dx, dy);
+      if constexpr (COORD) {
+        const float4 t1 = tp[1], t2 = tp[2], t3 = tp[3];
+        mCo0 = ffma(dy, t2.w, ffma(dx, t2.z, t1.w));
+        mCo1 = ffma(dy, t3.y, ffma(dx, t3.x, t2.x));
+        mCo2 = ffma(dy, t3.w, ffma(dx, t3.z, t2.y));
+      }
+      if constexpr (DEPTH) {
+        const float4 t0 = tp[0];
+        mDepth = fadd(t0.y, ffma(t0.z, dx, fmul(t0.w, dy)));
+      }
+    }
+  }
   if (inside) {
     p.n_contrib[(size_t)v * 2 * N + pix_id] = last_contributor;
     p.n_contrib[(size_t)v * 2 * N + N + pix_id] = max_contributor;
