@@ -401,7 +401,8 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   const int ns = geograd ? 32 : 16;
 
   // temp: gradient records + per-(view,Gaussian) partials
-  size_t grec_bytes = ((size_t)(R ? R : 1) * ns * sizeof(float) + 255) & ~size_t(255);
+  const int rec_floats = blend_bwd_record_floats(geograd);
+  size_t grec_bytes = ((size_t)(R ? R : 1) * rec_floats * sizeof(float) + 255) & ~size_t(255);
   size_t part_bytes = VP * 16 * sizeof(float);
   size_t sums_bytes = VP * (ns == 16 ? 12 : 28) * sizeof(float);
   char* tmp = temp_alloc(temp_user, grec_bytes + part_bytes + sums_bytes + 512);
@@ -427,7 +428,7 @@ int igs_rasterize_backward(const igs_backward_args* a, igs_alloc_fn temp_alloc, 
   }
 
   GatherBwdParams gp;
-  gp.P = P; gp.V = V; gp.W = W; gp.H = H; gp.ns = ns; gp.capacity = R; gp.skip_geo = 0; gp.focal_x = focal_x; gp.focal_y = focal_y;
+  gp.P = P; gp.V = V; gp.W = W; gp.H = H; gp.ns = ns; gp.rec_floats = rec_floats; gp.capacity = R; gp.skip_geo = 0; gp.focal_x = focal_x; gp.focal_y = focal_y;
   gp.tan_fovx = a->tan_fovx; gp.tan_fovy = a->tan_fovy; gp.kernel_size = a->kernel_size;
   gp.means3D = a->means3D; gp.cams = G.cams; gp.cov3D = G.cov3D; gp.eig = G.eig; gp.head = G.head; gp.radii = G.radii;
   gp.tiles = G.tiles; gp.rank = G.rank; gp.sorted_gid = G.sval[(hv.flags >> 8) & 1]; gp.inst_off = G.inst_off; gp.clamped = G.clamped; gp.grec = grec; gp.sums = sums;

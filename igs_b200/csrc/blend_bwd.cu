@@ -477,7 +477,7 @@ __device__ __forceinline__ void sts128_at(uint32_t addr, float a, float b, float
 template <int BATCH, int MINB, int CAP, bool MASK>
 __global__ void __launch_bounds__(256, MINB)
 blend_bwd2_kernel(BlendBwdParams p) {
-  constexpr int NS = 16;  // floats per gradient record in global memory
+  constexpr int NS = 12;  // floats per gradient record in global memory: the ten sums + 2 pad (48 bytes; was 64)
   constexpr int AS = 12;  // accumulator stride per batch slot (10 values + 2 pad words: 16-byte rows)
   constexpr int G = BWD2_GROUP;
   static_assert(BATCH <= 255 && BATCH % 32 == 0, "hit queue entries are bytes; whole 32-entry segments");
@@ -785,12 +785,11 @@ blend_bwd2_kernel(BlendBwdParams p) {
     }
     const int more = __syncthreads_or(qn > r0 + (uint32_t)CAP);
     // ---- 3. one dense record per instance of this batch: sum the 8 warps' accumulator rows of this round ----
-    // 16 bytes of a record per thread: three quarters come from the accumulators (values 0-9; words 10, 11 are pad
-    // and stay zero), the fourth is zero so that every 32-byte sector is written whole
-    for (uint32_t f = threadIdx.x; f < nb * 4; f += 256) {
-      const uint32_t sl = f >> 2, q4 = f & 3;
+    // 16 bytes of a record per thread (values 0-9; words 10, 11 are pad)
+    for (uint32_t f = threadIdx.x; f < nb * 3; f += 256) {
+      const uint32_t sl = f / 3u, q4 = f - sl * 3u;
       float4 sum = make_float4(0, 0, 0, 0);
-      if (q4 < 3) {
+      {
         const uint2 iv = *reinterpret_cast<const uint2*>(inv_cur + sl * 8u);
 #pragma unroll
         for (int ww = 0; ww < 8; ww++) {   // warp order, as before: absent rows were zeros then and are skipped now
@@ -817,7 +816,13 @@ blend_bwd2_kernel(BlendBwdParams p) {
   }
 }
 
-int blend_bwd_record_floats(bool geograd) { return geograd ? 32 : 16; }
+static int colour_bwd_impl() {   // IGS_BWD_IMPL=1 selects the first-generation colour-only kernel (reduction per pair); default: two-pass kernel
+  static const int impl = [] { const char* e = getenv("IGS_BWD_IMPL"); return e ? atoi(e) : 2; }();
+  return impl;
+}
+
+// floats per gradient record written by the kernel launch_blend_bwd selects (the stride of BlendBwdParams::grec)
+int blend_bwd_record_floats(bool geograd) { return geograd ? 32 : (colour_bwd_impl() >= 2 ? 12 : 16); }
 
 template <bool C, bool D, bool N, bool G, int MINB>
 static void launch_one(const BlendBwdParams& p, int nblocks, cudaStream_t s) {
@@ -849,8 +854,7 @@ void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bo
   // IGS_BWD_OCC=4 selects the 64-register / 96-instance-batch build of the colour-only kernel (4 CTAs/SM)
   static const int occ = [] { const char* e = getenv("IGS_BWD_OCC"); return e ? atoi(e) : 4; }();
   if (!geograd || (!coord && !depth)) {
-    // IGS_BWD_IMPL=1 selects the first-generation colour-only kernel (reduction per pair); default: two-pass kernel
-    static const int impl = [] { const char* e = getenv("IGS_BWD_IMPL"); return e ? atoi(e) : 2; }();
+    const int impl = colour_bwd_impl();
     static const int cfg = [] { const char* e = getenv("IGS_BWD2_CFG"); return e ? atoi(e) : 0; }();
     if (impl >= 2) {
       // default: 128-instance batches with 48 accumulator rows per warp (3 CTAs/SM): half the block barriers of the

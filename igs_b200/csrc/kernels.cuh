@@ -67,7 +67,8 @@ struct BlendBwdParams {
 
 struct GatherBwdParams {
   int P, V, W, H;
-  int ns;  // floats per record (16 or 32)
+  int ns;  // record layout: 16 = ten colour-only sums, 32 = with the geometry sums
+  int rec_floats;  // stride of grec in floats (12 / 16 for ns == 16, 32 for ns == 32): blend_bwd_record_floats()
   uint32_t capacity;  // emission slots the record buffer holds (R)
   float focal_x, focal_y, tan_fovx, tan_fovy, kernel_size;
   int skip_geo;       // set by the launcher: 1 = colour-only records, the normal / plane block is skipped (preprocess_bwd.cu)
@@ -130,6 +131,7 @@ void launch_decode_keys(uint32_t R, uint32_t tiles_per_view, uint32_t P, const u
                         cudaStream_t s);
 bool blend_fwd_writes_hitmask();   // whether the forward kernel in use fills BlendFwdParams::hitmask (IGS_HITMASK=0: off)
 void launch_blend_fwd(const BlendFwdParams& p, int V, bool coord, bool depth, cudaStream_t s);
+int blend_bwd_record_floats(bool geograd);   // stride (floats) of the gradient records the selected backward kernel writes
 void launch_blend_bwd(const BlendBwdParams& p, int V, bool coord, bool depth, bool geograd, cudaStream_t s);
 void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s);
 void launch_finish_bwd(const FinishBwdParams& p, cudaStream_t s);

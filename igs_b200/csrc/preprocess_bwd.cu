@@ -31,12 +31,12 @@ namespace igs {
 // positions are walked in depth-sorted order, so neighbouring threads read neighbouring memory: NS/4 lanes per
 // position, one 16-byte part each.  Kept apart from gather_bwd_kernel (146 registers, 16 % occupancy) so that this
 // bandwidth-bound half runs at full occupancy; the k-order of the additions is the list order (deterministic).
-template <int NS>
+template <int NS>   // record stride in floats: 12 (two-pass colour kernel), 16 (first-generation colour kernel), 32 (geometry)
 __global__ void __launch_bounds__(256)
 sum_records_kernel(size_t VP, const uint32_t* __restrict__ inst_off, const float* __restrict__ grec,
                    float* __restrict__ sums, uint32_t capacity) {
   constexpr int LANES = NS / 4;                // 16-byte parts per record
-  constexpr int PARTS = NS == 16 ? 3 : 7;      // parts that carry values (10 / 25 floats)
+  constexpr int PARTS = NS <= 16 ? 3 : 7;      // parts that carry values (10 / 25 floats)
   const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
   const size_t pos = t / LANES;
   const int part = (int)(t % LANES);
@@ -576,7 +576,8 @@ void launch_gather_bwd(const GatherBwdParams& p, cudaStream_t s) {
   if (p.P <= 0) return;
   const size_t VP = (size_t)p.V * p.P;
   count_launch(2);
-  if (p.ns == 16) sum_records_kernel<16><<<(unsigned)((VP * 4 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums, p.capacity);
+  if (p.ns == 16 && p.rec_floats == 12) sum_records_kernel<12><<<(unsigned)((VP * 3 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums, p.capacity);
+  else if (p.ns == 16) sum_records_kernel<16><<<(unsigned)((VP * 4 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums, p.capacity);
   else sum_records_kernel<32><<<(unsigned)((VP * 8 + 255) / 256), 256, 0, s>>>(VP, p.inst_off, p.grec, p.sums, p.capacity);
   GatherBwdParams q = p;
   q.skip_geo = p.ns == 16 ? 1 : 0;   // colour-only records: every geometry cotangent is zero
