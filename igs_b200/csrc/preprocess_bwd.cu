@@ -29,7 +29,7 @@ namespace igs {
 
 // Sum of each (view, Gaussian)'s gradient records.  Records of one Gaussian are consecutive (emission slots), and
 // positions are walked in depth-sorted order, so neighbouring threads read neighbouring memory: NS/4 lanes per
-// position, one 16-byte part each.  Kept apart from gather_bwd_kernel (146 registers, 16 % occupancy) so that this
+// position, one 16-byte part each.  Kept apart from gather_bwd_kernel (128 registers, 4 CTAs of 128 threads per SM) so that this
 // bandwidth-bound half runs at full occupancy; the k-order of the additions is the list order (deterministic).
 template <int NS>   // record stride in floats: 12 (two-pass colour kernel), 16 (first-generation colour kernel), 32 (geometry)
 __global__ void __launch_bounds__(256)
@@ -111,7 +111,7 @@ gather_bwd_kernel(GatherBwdParams p) {
   // A visible Gaussian that contributed to no pixel (hidden behind opaque ones, or below 1/255 everywhere) has an
   // all-zero record sum, and every output below is linear in it: its partial is exactly zero (the |grad| accumulator
   // s[5] >= 0 is zero only if every value is).  Skipping the chain for them matters because this kernel is latency
-  // bound (146 registers).
+  // bound (128 registers).
   {
     float nz = 0.0f;
 #pragma unroll
