@@ -2,7 +2,9 @@
 first-generation kernel (IGS_BWD_IMPL=1) compute the same gradients as the default build on a full-size case.  The
 variants differ only in how a tile's instance list is cut into batches and rounds, i.e. in the order of a few additions:
 the bar is 1e-4 max-normalised (ten times tighter than the bar against the reference).  Build 5 (128-instance batches,
-32 accumulator rows per warp) takes the multi-round write-out path on most dense tiles.
+32 accumulator rows per warp) takes the multi-round write-out path on most dense tiles.  IGS_HITMASK=0 makes the backward
+ignore the block-hit bytes the forward leaves and repeat the culls itself (the MASK = false build): the same pairs in the
+same order, so the gradients must be bit-identical.
 
 The switches are read once per process, so every variant runs in its own interpreter (tools/grad_noise_floor.py)."""
 import os
@@ -20,7 +22,7 @@ ROOT = Path(__file__).resolve().parent.parent
 
 def _run(env_extra, out):
     env = dict(os.environ)
-    for k in ("IGS_BWD2_CFG", "IGS_BWD_IMPL"):
+    for k in ("IGS_BWD2_CFG", "IGS_BWD_IMPL", "IGS_HITMASK"):
         env.pop(k, None)
     env.update(env_extra)
     r = subprocess.run([sys.executable, str(ROOT / "tools" / "grad_noise_floor.py"), "--case", "C2", "--no-ref", "--save", str(out)],
@@ -38,8 +40,9 @@ def base(tmp_path_factory):
 
 # (variant, bar): the batch builds only reorder additions; the first-generation kernel is a different formulation of the
 # same sums (per-pair reduction instead of per-pixel (aT, q) staging) and gets the bar used against the reference
-@pytest.mark.parametrize("variant,bar", [({"IGS_BWD2_CFG": "1"}, 1e-4), ({"IGS_BWD2_CFG": "5"}, 1e-4), ({"IGS_BWD_IMPL": "1"}, 1e-3)],
-                         ids=["batch64_rows64", "batch128_rows32", "first_generation"])
+@pytest.mark.parametrize("variant,bar", [({"IGS_BWD2_CFG": "1"}, 1e-4), ({"IGS_BWD2_CFG": "5"}, 1e-4), ({"IGS_BWD_IMPL": "1"}, 1e-3),
+                                         ({"IGS_HITMASK": "0"}, 0.0)],
+                         ids=["batch64_rows64", "batch128_rows32", "first_generation", "backward_culls_by_itself"])
 def test_backward_variants_agree_with_the_default_build(cuda_dev, base, tmp_path, variant, bar):
     sys.path.insert(0, str(ROOT / "tests"))
     import fullsize
