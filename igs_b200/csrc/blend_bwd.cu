@@ -752,8 +752,8 @@ blend_bwd2_kernel(BlendBwdParams p) {
           r0 += st.y;
           r1 = fmaf(st.y, (float)c - 3.5f, r1);
           r2 = fmaf(st.y, ((float)c - 3.5f) * ((float)c - 3.5f), r2);
-          b3 += fabsf(st.y * fmaf(-a.z, (float)c, ub));
-          b4 += fabsf(st.y * fmaf(-a.w, (float)c, wb));
+          b3 = fmaf(fabsf(st.y), fabsf(fmaf(-a.z, (float)c, ub)), b3);   // |q u| = |q| |u|: the absolute values ride on the FFMA's operands
+          b4 = fmaf(fabsf(st.y), fabsf(fmaf(-a.w, (float)c, wb)), b4);
         }
         R0[r] = r0; R1[r] = r1; R2[r] = r2;
       }
