@@ -497,7 +497,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
   extern __shared__ __align__(16) float s_dyn[];
   float* s_acc = s_dyn;                                             // [8 warps][CAP queue positions of a round][AS]
   float* s_stage = s_dyn + 8 * CAP * AS;                            // [8 warps][G][33] float2 (aT, q)
-  float4* s_pix = reinterpret_cast<float4*>(s_stage + 8 * G * BWD2_STRIDE * 2);  // [8 warps][34] {dLp r, g, b, -}
+  float4* s_pix = reinterpret_cast<float4*>(s_stage + 8 * G * BWD2_STRIDE * 2);  // [8 warps][34] {dLp r, g, b, 1}
 
   const int tiles = p.tiles_x * p.tiles_y;
   const int gt = blockIdx.x;
@@ -549,7 +549,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
     dLp0 = g[pix_id]; dLp1 = g[N + pix_id]; dLp2 = g[2 * N + pix_id];
     if (p.dL_alpha) dL_dalpha = p.dL_alpha[(size_t)v * N + pix_id];
   }
-  sts128_at(pix_base + ((uint32_t)lane + ((uint32_t)lane >> 4)) * 16, dLp0, dLp1, dLp2, 0.0f);
+  sts128_at(pix_base + ((uint32_t)lane + ((uint32_t)lane >> 4)) * 16, dLp0, dLp1, dLp2, 1.0f);   // (b, 1): multiplicand of (aT, q)
   // The alpha cotangent and the background enter dL/dopacity of instance i only as
   //   T_final / (1 - alpha_i) * (dL/dalpha - bg . dL/dpixel):
   // the reference's accumulated-alpha recurrence (backward.cu:972-975) telescopes, 1 - accum_alpha_rec = T_final / T_behind.
@@ -734,28 +734,43 @@ blend_bwd2_kernel(BlendBwdParams p) {
       const float gx = a.x - bx0;
       const float gy = (a.y - by0) - (float)(2u * h);
       const float gxc = gx - 3.5f, gyc = gy - 0.5f;
-      float v0 = 0, v1 = 0, v2 = 0, b3 = 0, b4 = 0;
-      float R0[2], R1[2], R2[2];
+      // The kernel is issue bound: the sums are advanced in fp32x2 pairs — (v0, v1) += aT (dLr, dLg),
+      // (v2, S0) += (aT, q) (dLb, 1) straight from the staged (aT, q) pair, (u, w) = (ub, wb) - c (cx, cy) — 7 instead of 10
+      // arithmetic instructions per pixel; every element is still one fused multiply-add.
+      float b3 = 0, b4 = 0;
+      f32x2 V01 = pack2(0.0f, 0.0f);
+      f32x2 VR[2];      // per pixel row: (sum aT dLb, sum q)
+      float R1[2], R2[2];
+      const f32x2 ncxy = pack2(-a.z, -a.w);
 #pragma unroll
       for (int r = 0; r < 2; r++) {
         const float ddy = gy - (float)r;
-        const float ub = fmaf(a.z, gx, a.w * ddy), wb = fmaf(a.w, gx, bq.x * ddy);  // cx dx + cy dy, cy dx + cz dy at c = 0
-        float r0 = 0, r1 = 0, r2 = 0;
+        const f32x2 ubwb = pack2(fmaf(a.z, gx, a.w * ddy), fmaf(a.w, gx, bq.x * ddy));  // cx dx + cy dy, cy dx + cz dy at c = 0
+        f32x2 vr = pack2(0.0f, 0.0f);
+        float r1 = 0, r2 = 0;
 #pragma unroll
         for (int c = 0; c < 8; c++) {
           const int s = r * 8 + c;
           const float2 st = lds64_at(stage_rd + s * 8);
           const float4 dl = lds128_at(pix_rd + s * 16);
-          v0 = fmaf(st.x, dl.x, v0);
-          v1 = fmaf(st.x, dl.y, v1);
-          v2 = fmaf(st.x, dl.z, v2);
-          r0 += st.y;
+          V01 = fma2(pack2(st.x, st.x), pack2(dl.x, dl.y), V01);
+          vr = fma2(pack2(st.x, st.y), pack2(dl.z, dl.w), vr);
           r1 = fmaf(st.y, (float)c - 3.5f, r1);
           r2 = fmaf(st.y, ((float)c - 3.5f) * ((float)c - 3.5f), r2);
-          b3 = fmaf(fabsf(st.y), fabsf(fmaf(-a.z, (float)c, ub)), b3);   // |q u| = |q| |u|: the absolute values ride on the FFMA's operands
-          b4 = fmaf(fabsf(st.y), fabsf(fmaf(-a.w, (float)c, wb)), b4);
+          float u, wv;
+          unpack2(fma2(ncxy, pack2((float)c, (float)c), ubwb), u, wv);
+          b3 = fmaf(fabsf(st.y), fabsf(u), b3);   // |q u| = |q| |u|: the absolute values ride on the FFMA's operands
+          b4 = fmaf(fabsf(st.y), fabsf(wv), b4);
         }
-        R0[r] = r0; R1[r] = r1; R2[r] = r2;
+        VR[r] = vr; R1[r] = r1; R2[r] = r2;
+      }
+      float v0, v1, v2, R0[2];
+      unpack2(V01, v0, v1);
+      {
+        float va, vb;
+        unpack2(VR[0], va, R0[0]);
+        unpack2(VR[1], vb, R0[1]);
+        v2 = va + vb;
       }
       const float S0 = R0[0] + R0[1], Sx = R1[0] + R1[1], Sxx = R2[0] + R2[1];
       const float Sy = 0.5f * (R0[1] - R0[0]), Sxy = 0.5f * (R1[1] - R1[0]);
