@@ -686,7 +686,7 @@ blend_bwd2_kernel(BlendBwdParams p) {
     for (uint32_t g0 = r0; g0 < rend; g0 += G) {
       const uint32_t ng = min((uint32_t)G, rend - g0);
       // ---- pass 1: lanes = pixels, one hit per iteration ----
-#pragma unroll 2
+#pragma unroll 8
       for (uint32_t i = 0; i < ng; i++) {
         const uint32_t kk = queue[g0 + i];
         const uint32_t ak = rec_base + kk * 16;
